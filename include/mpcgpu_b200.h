@@ -1,0 +1,118 @@
+/*
+ * mpcgpu_b200.h -- C ABI of the B200-native (sm_100a) linear-system hot path of MPCGPU:
+ *     form_schur_system  (Schur complement S, symmetric-stair preconditioner Pinv, gamma, G^-1)
+ *     pcg                (block-tridiagonal preconditioned conjugate gradient)
+ * plus the fused KKT solve (S / Pinv never materialised in HBM).
+ *
+ * Drop-in boundary: every entry point cites the reference interface it replaces (paths
+ * relative to the MPCGPU checkout).  Plain pointers and sizes only; no CUDA or torch types
+ * in the signatures (a stream is passed as `void*` holding a cudaStream_t, NULL = legacy
+ * default stream, which is what the reference launches on: include/pcg/sqp.cuh:275,
+ * include/pcg/linsys_setup.cuh:656).
+ *
+ * Conventions inherited from the reference:
+ *   - caller owns every device buffer; nothing is allocated per call;
+ *   - all blocks are COLUMN-MAJOR; buffer sizes as include/pcg/sqp.cuh:54-58,111,130:
+ *       G     (s*s+c*c)*N - c*c      [Q_k | R_k] per knot (last knot Q only)   IN/OUT (G -> G^-1)
+ *       C     (s*s+s*c)*(N-1)        [Abar_k | Bbar_k], Abar = -A, Bbar = -B
+ *       g     (s+c)*N - c            [q_k | r_k]
+ *       c     s*N                    constraint residuals (c[0:s] never read)
+ *       S,Pinv 3*s*s*N               [N][3][s*s] block rows (left, diag, right)
+ *       gamma, lambda  s*N
+ *   - batched calls: instance b's buffer starts at base + b * <size above> (tight packing);
+ *     batch == 1 is exactly the reference's single-instance layout;
+ *   - d_lambda is IN (warm start, include/mpcsim.cuh:227,383) and OUT;
+ *   - PCG non-convergence is data (max_iter_exit = 1), not an error
+ *     (include/pcg/sqp.cuh:277,289);
+ *   - return value: 0 on success, otherwise a cudaError_t value
+ *     (cudaErrorInvalidValue for unsupported sizes); mpcgpu_b200_last_error() has the text.
+ *   - supported sizes in this build: state_size 14, control_size 7 (Kuka IIWA,
+ *     examples/track_iiwa_pcg.cu:16-17), 1 <= knot_points <= 512, fp32
+ *     (linsys_t, include/common/settings.cuh:49-57).
+ * There is NO CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef MPCGPU_B200_H
+#define MPCGPU_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MPCGPU_B200_ABI_VERSION 1
+
+/* ABI version of the loaded library. */
+int mpcgpu_b200_abi_version(void);
+
+/* Text of the last error raised on the calling thread ("" if none). */
+const char* mpcgpu_b200_last_error(void);
+
+/* Bytes of device scratch `d_ws` the pcg / kkt_solve entry points want for these sizes.
+ * Replaces the per-solve scratch the reference slot allocates (d_r, d_p, d_v_temp,
+ * d_eta_new_temp: include/pcg/sqp.cuh:134-138).  May be 0 (cluster kernels keep all
+ * iteration state on-chip); d_ws may then be NULL. */
+size_t mpcgpu_b200_workspace_bytes(uint32_t state_size, uint32_t control_size,
+                                   uint32_t knot_points, uint32_t batch);
+
+/* form_schur_system<float>  (include/pcg/linsys_setup.cuh:620-657; kernel :565-612).
+ * Writes S, Pinv (including zeros in the four corner blocks the reference leaves
+ * unwritten), gamma, and overwrites G with G^-1 in place (linsys_setup.cuh:372-380). */
+int mpcgpu_b200_schur_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                          uint32_t batch, float* d_G, const float* d_C, const float* d_g,
+                          const float* d_c, float rho, float* d_S, float* d_Pinv,
+                          float* d_gamma, void* stream);
+
+/* pcg<float, STATE_SIZE, KNOT_POINTS>  (GBD-PCG gpu_pcg.cuh; launch + argument list at
+ * include/pcg/sqp.cuh:142-166,275; result read-back :276-277).
+ * d_iters[b]: completed iterations; d_max_iter_exit[b]: 1 when max_iter was exhausted.
+ * Exit test |r . Pinv r| < exit_tol (absolute). */
+int mpcgpu_b200_pcg_f32(uint32_t state_size, uint32_t knot_points, uint32_t batch,
+                        const float* d_S, const float* d_Pinv, const float* d_gamma,
+                        float* d_lambda, uint32_t max_iter, float exit_tol, uint32_t* d_iters,
+                        uint8_t* d_max_iter_exit, void* d_ws, void* stream);
+
+/* Fused form_schur_system + pcg (include/pcg/sqp.cuh:243-277 as ONE launch): reads
+ * G, C, g, c, lambda0; writes lambda, G^-1, iters, flags.  S and Pinv stay on-chip. */
+int mpcgpu_b200_kkt_solve_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                              uint32_t batch, float* d_G, const float* d_C, const float* d_g,
+                              const float* d_c, float rho, float* d_lambda, uint32_t max_iter,
+                              float exit_tol, uint32_t* d_iters, uint8_t* d_max_iter_exit,
+                              void* d_ws, void* stream);
+
+/* Reference-STYLE PCG (one CTA per knot, 4 grid barriers per iteration, cooperative launch):
+ * our restatement of the reference kernel's structure, kept as the in-repo
+ * comparison kernel and as the kernel behind the header shim's pcg<T,S,N>.  batch == 1.
+ * d_ws: at least (2*s*N + 2*N) floats (d_r, d_p, d_v_temp, d_eta_new_temp). */
+int mpcgpu_b200_pcg_refstyle_f32(uint32_t state_size, uint32_t knot_points, const float* d_S,
+                                 const float* d_Pinv, const float* d_gamma, float* d_lambda,
+                                 uint32_t max_iter, float exit_tol, uint32_t* d_iters,
+                                 uint8_t* d_max_iter_exit, void* d_ws, void* stream);
+
+/* ---- host-buffer solver object (the call a user of the reference's solver slot makes
+ * when the KKT blocks live on the host, cf. the QDLDL slot's PCIe round trip
+ * include/qdldl/sqp.cuh:268-273).  Owns persistent device buffers and streams; nothing is
+ * allocated per solve. ---- */
+typedef struct mpcgpu_b200_solver mpcgpu_b200_solver;
+
+int mpcgpu_b200_solver_create(mpcgpu_b200_solver** out, int device, uint32_t state_size,
+                              uint32_t control_size, uint32_t knot_points, uint32_t max_batch);
+void mpcgpu_b200_solver_destroy(mpcgpu_b200_solver* solver);
+
+/* Host buffers (pinned for full PCIe speed; pageable works).  h_lambda IN/OUT.
+ * h_Ginv may be NULL (G^-1 not copied back).  Copies are pipelined with the kernels in
+ * chunks; returns after all results are in the host buffers. */
+int mpcgpu_b200_solver_solve_host_f32(mpcgpu_b200_solver* solver, uint32_t batch,
+                                      const float* h_G, const float* h_C, const float* h_g,
+                                      const float* h_c, float rho, float* h_lambda,
+                                      uint32_t max_iter, float exit_tol, uint32_t* h_iters,
+                                      uint8_t* h_max_iter_exit, float* h_Ginv);
+
+/* Kernel launches issued by this library since load (all threads). */
+uint64_t mpcgpu_b200_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MPCGPU_B200_H */

@@ -1,0 +1,14 @@
+"""mpcgpu_b200 -- B200-native (sm_100a) linear-system hot path of MPCGPU:
+Schur-complement formation (S, symmetric-stair preconditioner, gamma) and the
+block-tridiagonal PCG solve, behind the reference's pluggable linear-solver interface.
+
+Layout: csrc/ (CUDA kernels + C ABI -> libmpcgpu_b200.so), api.py (host-side mirror of the
+reference interface over that ABI), shim/ (drop-in headers for the reference's own
+include/pcg/sqp.cuh), synth.py (seeded synthetic KKT blocks).
+"""
+from . import synth  # noqa: F401
+from .api import (HostSolver, MpcGpuError, PcgConfig, form_schur_system, kkt_solve,  # noqa: F401
+                  launch_count, lib, pcg, sizes)
+
+__all__ = ["HostSolver", "MpcGpuError", "PcgConfig", "form_schur_system", "kkt_solve", "pcg",
+           "sizes", "synth", "lib", "launch_count"]

@@ -1,0 +1,201 @@
+"""Host-side mirror of the reference's linear-solver interface, over the C ABI
+(``include/mpcgpu_b200.h`` -> ``libmpcgpu_b200.so``).
+
+Same names, argument order and meaning as the reference (torch CUDA tensors stand in for the
+reference's raw device pointers; torch is plumbing for device memory / streams only):
+
+* :func:`form_schur_system` -- ``include/pcg/linsys_setup.cuh:620-657``
+* :func:`pcg`               -- launch at ``include/pcg/sqp.cuh:275`` + read-back ``:276-277``
+* :func:`kkt_solve`         -- the two fused (``include/pcg/sqp.cuh:243-277`` as one launch)
+* :class:`PcgConfig`        -- ``pcg_config<T>`` (``include/mpcsim.cuh:250-253``)
+* :class:`HostSolver`       -- solver object for KKT blocks that live in host memory
+
+There is NO CPU fallback: if the CUDA library is missing or no GPU is present, every
+compute entry point raises.
+"""
+import ctypes
+import os
+from dataclasses import dataclass
+
+import torch
+
+from . import build as _build
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class MpcGpuError(RuntimeError):
+    pass
+
+
+def lib():
+    """Load (once) the in-tree CUDA library; raises loudly if it is absent."""
+    global _LIB
+    if _LIB is None:
+        path = _build.LIB
+        if not os.path.exists(path):
+            raise MpcGpuError(
+                "%s not found: build it with `python -m mpcgpu_b200.build` "
+                "(there is no CPU fallback)" % path)
+        L = ctypes.CDLL(path)
+        L.mpcgpu_b200_last_error.restype = ctypes.c_char_p
+        L.mpcgpu_b200_workspace_bytes.restype = ctypes.c_size_t
+        L.mpcgpu_b200_launch_count.restype = ctypes.c_uint64
+        if L.mpcgpu_b200_abi_version() != 1:
+            raise MpcGpuError("ABI version mismatch")
+        _LIB = L
+    return _LIB
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise MpcGpuError("%s failed (cudaError %d): %s"
+                          % (what, rc, lib().mpcgpu_b200_last_error().decode()))
+
+
+def _ptr(t, dtype, what, numel=None):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise MpcGpuError("%s must be a CUDA tensor (no CPU fallback)" % what)
+    if t.dtype != dtype or not t.is_contiguous():
+        raise MpcGpuError("%s must be contiguous %s" % (what, dtype))
+    if numel is not None and t.numel() < numel:
+        raise MpcGpuError("%s too small: %d < %d elements" % (what, t.numel(), numel))
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def sizes(s, c, N):
+    """Element counts of the reference buffers (include/pcg/sqp.cuh:54-58,111,130)."""
+    return {
+        "G": (s * s + c * c) * N - c * c, "C": (s * s + s * c) * (N - 1),
+        "g": (s + c) * N - c, "c": s * N, "S": 3 * s * s * N, "Pinv": 3 * s * s * N,
+        "gamma": s * N, "lambda": s * N,
+    }
+
+
+@dataclass
+class PcgConfig:
+    """pcg_config<T> (include/mpcsim.cuh:250-253)."""
+    pcg_block: int = 128
+    pcg_exit_tol: float = 1e-4
+    pcg_max_iter: int = 10000   # include/common/settings.cuh:133 (this fork)
+
+
+def form_schur_system(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, d_c,
+                      d_S, d_Pinv, d_gamma, rho, batch=1):
+    """form_schur_system<float>: writes d_S, d_Pinv, d_gamma; d_G_dense becomes G^-1."""
+    s, c, N = state_size, control_size, knot_points
+    z = sizes(s, c, N)
+    f = torch.float32
+    rc = lib().mpcgpu_b200_schur_f32(
+        ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
+        _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
+        _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
+        _ptr(d_g, f, "d_g", z["g"] * batch), _ptr(d_c, f, "d_c", z["c"] * batch),
+        ctypes.c_float(rho), _ptr(d_S, f, "d_S", z["S"] * batch),
+        _ptr(d_Pinv, f, "d_Pinv", z["S"] * batch), _ptr(d_gamma, f, "d_gamma", z["gamma"] * batch),
+        _stream())
+    _check(rc, "form_schur_system")
+
+
+def pcg(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_pcg_iters, d_pcg_exit,
+        config: PcgConfig, batch=1, refstyle=False, d_ws=None):
+    """pcg<float,STATE_SIZE,KNOT_POINTS>: d_lambda in (warm start) / out.
+    d_pcg_iters: uint32 (int32 tensor storage), d_pcg_exit: uint8/bool tensor."""
+    s, N = state_size, knot_points
+    z = sizes(s, 7, N)
+    f = torch.float32
+    if d_pcg_iters.dtype != torch.int32 or d_pcg_exit.dtype not in (torch.uint8, torch.bool):
+        raise MpcGpuError("d_pcg_iters must be int32 and d_pcg_exit uint8/bool")
+    args = [_ptr(d_S, f, "d_S", z["S"] * batch), _ptr(d_Pinv, f, "d_Pinv", z["S"] * batch),
+            _ptr(d_gamma, f, "d_gamma", z["gamma"] * batch),
+            _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
+            ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+            _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", batch),
+            _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", batch)]
+    if refstyle:
+        if batch != 1:
+            raise MpcGpuError("reference-style kernel is single-instance")
+        need = lib().mpcgpu_b200_workspace_bytes(ctypes.c_uint32(s), ctypes.c_uint32(7),
+                                                 ctypes.c_uint32(N), ctypes.c_uint32(1))
+        if d_ws is None:
+            d_ws = torch.empty(need // 4, dtype=f, device=d_S.device)
+        rc = lib().mpcgpu_b200_pcg_refstyle_f32(
+            ctypes.c_uint32(s), ctypes.c_uint32(N), *args, _ptr(d_ws, f, "d_ws", need // 4), _stream())
+    else:
+        rc = lib().mpcgpu_b200_pcg_f32(ctypes.c_uint32(s), ctypes.c_uint32(N),
+                                       ctypes.c_uint32(batch), *args, None, _stream())
+    _check(rc, "pcg")
+
+
+def kkt_solve(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, d_c, rho,
+              d_lambda, d_pcg_iters, d_pcg_exit, config: PcgConfig, batch=1):
+    """Fused form_schur_system + pcg: d_G_dense -> G^-1, d_lambda in/out."""
+    s, c, N = state_size, control_size, knot_points
+    z = sizes(s, c, N)
+    f = torch.float32
+    rc = lib().mpcgpu_b200_kkt_solve_f32(
+        ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
+        _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
+        _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
+        _ptr(d_g, f, "d_g", z["g"] * batch), _ptr(d_c, f, "d_c", z["c"] * batch),
+        ctypes.c_float(rho), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
+        ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+        _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", batch),
+        _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", batch), None, _stream())
+    _check(rc, "kkt_solve")
+
+
+def launch_count():
+    return int(lib().mpcgpu_b200_launch_count())
+
+
+class HostSolver:
+    """Solver object over host (ideally pinned) buffers: H2D, fused solve and D2H are
+    pipelined in chunks inside the library (mpcgpu_b200_solver_* in the C ABI)."""
+
+    def __init__(self, state_size, control_size, knot_points, max_batch, device=0):
+        self.s, self.c, self.N, self.max_batch = state_size, control_size, knot_points, max_batch
+        self._h = ctypes.c_void_p()
+        rc = lib().mpcgpu_b200_solver_create(
+            ctypes.byref(self._h), ctypes.c_int(device), ctypes.c_uint32(state_size),
+            ctypes.c_uint32(control_size), ctypes.c_uint32(knot_points), ctypes.c_uint32(max_batch))
+        _check(rc, "solver_create")
+
+    @staticmethod
+    def _hp(t, dtype, n, what):
+        if t is None:
+            return None
+        if t.is_cuda or t.dtype != dtype or not t.is_contiguous() or t.numel() < n:
+            raise MpcGpuError("%s must be a contiguous host %s tensor with >= %d elements" % (what, dtype, n))
+        return ctypes.c_void_p(t.data_ptr())
+
+    def solve(self, h_G, h_C, h_g, h_c, rho, h_lambda, h_iters, h_exit, config: PcgConfig,
+              batch, h_Ginv=None):
+        z = sizes(self.s, self.c, self.N)
+        f = torch.float32
+        rc = lib().mpcgpu_b200_solver_solve_host_f32(
+            self._h, ctypes.c_uint32(batch),
+            self._hp(h_G, f, z["G"] * batch, "h_G"), self._hp(h_C, f, z["C"] * batch, "h_C"),
+            self._hp(h_g, f, z["g"] * batch, "h_g"), self._hp(h_c, f, z["c"] * batch, "h_c"),
+            ctypes.c_float(rho), self._hp(h_lambda, f, z["lambda"] * batch, "h_lambda"),
+            ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+            self._hp(h_iters, torch.int32, batch, "h_iters"),
+            self._hp(h_exit, torch.uint8, batch, "h_exit"),
+            self._hp(h_Ginv, f, z["G"] * batch, "h_Ginv"))
+        _check(rc, "solver_solve_host")
+
+    def close(self):
+        if self._h:
+            lib().mpcgpu_b200_solver_destroy(self._h)
+            self._h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

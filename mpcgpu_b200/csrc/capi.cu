@@ -1,0 +1,198 @@
+// capi.cu -- C ABI (include/mpcgpu_b200.h) and kernel dispatch.
+// No torch, no CPU fallback: every compute entry point launches sm_100a kernels or fails.
+#include "../../include/mpcgpu_b200.h"
+
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+
+#include "kernels.cuh"
+#include "refstyle_pcg.cuh"
+
+using namespace mpcb200;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<uint64_t> g_launches{0};
+
+int fail(cudaError_t e, const char* what) {
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return (int)e;
+}
+int bad(const char* what) {
+    g_err = what;
+    return (int)cudaErrorInvalidValue;
+}
+
+enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2 };
+
+template <class CF, int KIND>
+cudaError_t launch(const BatchArgs& a, cudaStream_t st) {
+    auto kern = (KIND == K_SCHUR) ? schur_kernel<CF> : (KIND == K_PCG) ? pcg_kernel<CF> : fused_kernel<CF>;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (configured_dev != dev) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        if (CF::CL > 8) {
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            if (e != cudaSuccess) return e;
+        }
+        configured_dev = dev;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)a.batch * CF::CL, 1, 1);
+    cfg.blockDim = dim3(CF::NT, 1, 1);
+    cfg.dynamicSmemBytes = CF::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CF::CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, kern, a);
+    if (e == cudaSuccess) g_launches.fetch_add(1, std::memory_order_relaxed);
+    return e;
+}
+
+// (KPC, CL) tiling: N <= KPC*CL.  MPCGPU_B200_KPC=16 selects the low-latency tiling
+// (half the knots per CTA, twice the cluster) where it exists.
+template <int KIND>
+cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
+    static const int pref_kpc = [] {
+        const char* e = getenv("MPCGPU_B200_KPC");
+        return e ? atoi(e) : 32;
+    }();
+    const int N = a.N;
+    if (pref_kpc == 16) {
+        if (N <= 16) return launch<Cfg<14, 7, 16, 1>, KIND>(a, st);
+        if (N <= 32) return launch<Cfg<14, 7, 16, 2>, KIND>(a, st);
+        if (N <= 64) return launch<Cfg<14, 7, 16, 4>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<14, 7, 16, 8>, KIND>(a, st);
+        if (N <= 256) return launch<Cfg<14, 7, 16, 16>, KIND>(a, st);
+    }
+    if (N <= 32) return launch<Cfg<14, 7, 32, 1>, KIND>(a, st);
+    if (N <= 64) return launch<Cfg<14, 7, 32, 2>, KIND>(a, st);
+    if (N <= 128) return launch<Cfg<14, 7, 32, 4>, KIND>(a, st);
+    if (N <= 256) return launch<Cfg<14, 7, 32, 8>, KIND>(a, st);
+    if (N <= 512) return launch<Cfg<14, 7, 32, 16>, KIND>(a, st);
+    return cudaErrorInvalidValue;
+}
+
+BatchArgs make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
+    BatchArgs a;
+    memset(&a, 0, sizeof(a));
+    a.N = (int)N;
+    a.batch = (int)batch;
+    a.sG = (size_t)(s * s + c * c) * N - c * c;
+    a.sC = (size_t)(s * s + s * c) * (N - 1);
+    a.sg = (size_t)(s + c) * N - c;
+    a.sc = (size_t)s * N;
+    a.sS = (size_t)3 * s * s * N;
+    a.sv = (size_t)s * N;
+    return a;
+}
+
+bool sizes_ok(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
+    return s == 14 && c == 7 && N >= 1 && N <= 512 && batch >= 1 && batch <= (1u << 24);
+}
+
+// reference-style comparison kernel (cooperative, one CTA per knot)
+__global__ void refstyle_kernel(uint32_t s, uint32_t N, const float* d_S, const float* d_Pinv,
+                                const float* d_gamma, float* d_lambda, float* d_r, float* d_p,
+                                float* d_v, float* d_eta, uint32_t* d_iters, bool* d_exit,
+                                uint32_t max_iter, float tol) {
+    extern __shared__ float rs_smem[];
+    mpcb200_refstyle::pcg_body<float>(s, N, d_S, d_Pinv, d_gamma, d_lambda, d_r, d_p, d_v, d_eta,
+                                      d_iters, d_exit, max_iter, tol, rs_smem);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mpcgpu_b200_abi_version(void) { return MPCGPU_B200_ABI_VERSION; }
+
+const char* mpcgpu_b200_last_error(void) { return g_err.c_str(); }
+
+uint64_t mpcgpu_b200_launch_count(void) { return g_launches.load(); }
+
+size_t mpcgpu_b200_workspace_bytes(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
+    (void)c; (void)batch;
+    // only the reference-style comparison kernel needs global scratch
+    return sizeof(float) * ((size_t)2 * s * N + 2 * N);
+}
+
+int mpcgpu_b200_schur_f32(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, float* d_G,
+                          const float* d_C, const float* d_g, const float* d_c, float rho,
+                          float* d_S, float* d_Pinv, float* d_gamma, void* stream) {
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_schur_f32: unsupported sizes (need s=14,c=7,1<=N<=512)");
+    if (!d_G || (N > 1 && !d_C) || !d_g || !d_c || !d_S || !d_Pinv || !d_gamma) return bad("mpcgpu_b200_schur_f32: null pointer");
+    BatchArgs a = make_args(s, c, N, batch);
+    a.G = d_G; a.C = d_C; a.g = d_g; a.c = d_c; a.rho = rho;
+    a.S = d_S; a.Pinv = d_Pinv; a.gamma = d_gamma;
+    cudaError_t e = dispatch<K_SCHUR>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_schur_f32");
+}
+
+int mpcgpu_b200_pcg_f32(uint32_t s, uint32_t N, uint32_t batch, const float* d_S,
+                        const float* d_Pinv, const float* d_gamma, float* d_lambda,
+                        uint32_t max_iter, float exit_tol, uint32_t* d_iters,
+                        uint8_t* d_max_iter_exit, void* d_ws, void* stream) {
+    (void)d_ws;
+    if (!sizes_ok(s, 7, N, batch)) return bad("mpcgpu_b200_pcg_f32: unsupported sizes (need s=14,1<=N<=512)");
+    if (!d_S || !d_Pinv || !d_gamma || !d_lambda || !d_iters || !d_max_iter_exit) return bad("mpcgpu_b200_pcg_f32: null pointer");
+    BatchArgs a = make_args(s, 7, N, batch);
+    a.S = const_cast<float*>(d_S); a.Pinv = const_cast<float*>(d_Pinv); a.gamma = const_cast<float*>(d_gamma);
+    a.lambda = d_lambda; a.max_iter = max_iter; a.exit_tol = exit_tol;
+    a.iters = d_iters; a.exits = d_max_iter_exit;
+    cudaError_t e = dispatch<K_PCG>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_pcg_f32");
+}
+
+int mpcgpu_b200_kkt_solve_f32(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, float* d_G,
+                              const float* d_C, const float* d_g, const float* d_c, float rho,
+                              float* d_lambda, uint32_t max_iter, float exit_tol,
+                              uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws,
+                              void* stream) {
+    (void)d_ws;
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_kkt_solve_f32: unsupported sizes (need s=14,c=7,1<=N<=512)");
+    if (!d_G || (N > 1 && !d_C) || !d_g || !d_c || !d_lambda || !d_iters || !d_max_iter_exit) return bad("mpcgpu_b200_kkt_solve_f32: null pointer");
+    BatchArgs a = make_args(s, c, N, batch);
+    a.G = d_G; a.C = d_C; a.g = d_g; a.c = d_c; a.rho = rho;
+    a.lambda = d_lambda; a.max_iter = max_iter; a.exit_tol = exit_tol;
+    a.iters = d_iters; a.exits = d_max_iter_exit;
+    cudaError_t e = dispatch<K_FUSED>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_kkt_solve_f32");
+}
+
+int mpcgpu_b200_pcg_refstyle_f32(uint32_t s, uint32_t N, const float* d_S, const float* d_Pinv,
+                                 const float* d_gamma, float* d_lambda, uint32_t max_iter,
+                                 float exit_tol, uint32_t* d_iters, uint8_t* d_max_iter_exit,
+                                 void* d_ws, void* stream) {
+    if (s < 1 || s > 32 || N < 1) return bad("mpcgpu_b200_pcg_refstyle_f32: unsupported sizes");
+    if (!d_S || !d_Pinv || !d_gamma || !d_lambda || !d_iters || !d_max_iter_exit || !d_ws) return bad("mpcgpu_b200_pcg_refstyle_f32: null pointer");
+    float* d_r = (float*)d_ws;
+    float* d_p = d_r + (size_t)s * N;
+    float* d_v = d_p + (size_t)s * N;
+    float* d_eta = d_v + N;
+    bool* d_exit = reinterpret_cast<bool*>(d_max_iter_exit);
+    size_t smem = sizeof(float) * mpcb200_refstyle::smem_elems<float>(s);
+    void* args[] = {&s, &N, &d_S, &d_Pinv, &d_gamma, &d_lambda, &d_r, &d_p, &d_v, &d_eta,
+                    &d_iters, &d_exit, &max_iter, &exit_tol};
+    cudaError_t e = cudaLaunchCooperativeKernel((void*)refstyle_kernel, dim3(N), dim3(128), args,
+                                                smem, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(e, "mpcgpu_b200_pcg_refstyle_f32");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,136 @@
+// common.cuh -- shared helpers for the sm_100a KKT linear-system kernels.
+//
+// Thread mapping used everywhere in this directory ("row-owner" layout):
+//   one group of LPK=16 lanes per knot; lane i<STATE owns ROW i of every STATE x STATE
+//   block of that knot in registers.  Two knots share a warp, so all intra-knot
+//   synchronisation is __syncwarp(); cross-knot traffic goes through padded shared-memory
+//   tiles (row stride 16 floats = 64 B so a row is four LDS.128) and, across the CTAs of a
+//   thread-block cluster, through DSMEM.
+#pragma once
+#include <cuda_runtime.h>
+#include <cooperative_groups.h>
+#include <cstdint>
+
+namespace mpcb200 {
+
+namespace cg = cooperative_groups;
+
+constexpr int LPK = 16;  // lanes per knot (STATE <= 16)
+constexpr int LD = 16;   // padded leading dimension of shared-memory tiles (floats)
+
+// ---- cluster helpers (no-ops for CL == 1) ---------------------------------------------
+template <int CL>
+__device__ __forceinline__ void cluster_sync_all() {
+    if constexpr (CL == 1) {
+        __syncthreads();
+    } else {
+        cg::this_cluster().sync();
+    }
+}
+
+template <int CL>
+__device__ __forceinline__ unsigned cluster_rank() {
+    if constexpr (CL == 1) return 0u;
+    else return cg::this_cluster().block_rank();
+}
+
+template <int CL, typename P>
+__device__ __forceinline__ P* map_rank(P* p, unsigned rank) {
+    if constexpr (CL == 1) return p;
+    else return cg::this_cluster().map_shared_rank(p, rank);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ---- row tiles ------------------------------------------------------------------------
+// write my row (D values, zero padded to a multiple of 4) to dst + row*ld
+template <int D>
+__device__ __forceinline__ void publish_row(float* dst, int ld, int row, const float (&a)[D]) {
+    float4* d = reinterpret_cast<float4*>(dst + row * ld);
+#pragma unroll
+    for (int q = 0; q < (D + 3) / 4; q++) {
+        float4 v;
+        v.x = (4 * q + 0 < D) ? a[4 * q + 0] : 0.f;
+        v.y = (4 * q + 1 < D) ? a[4 * q + 1] : 0.f;
+        v.z = (4 * q + 2 < D) ? a[4 * q + 2] : 0.f;
+        v.w = (4 * q + 3 < D) ? a[4 * q + 3] : 0.f;
+        d[q] = v;
+    }
+}
+
+// read one padded row (broadcast within the knot group) into registers
+template <int D>
+__device__ __forceinline__ void load_row(float (&r)[D], const float* src) {
+    const float4* s = reinterpret_cast<const float4*>(src);
+#pragma unroll
+    for (int q = 0; q < (D + 3) / 4; q++) {
+        float4 v = s[q];
+        if (4 * q + 0 < D) r[4 * q + 0] = v.x;
+        if (4 * q + 1 < D) r[4 * q + 1] = v.y;
+        if (4 * q + 2 < D) r[4 * q + 2] = v.z;
+        if (4 * q + 3 < D) r[4 * q + 3] = v.w;
+    }
+}
+
+// c[j] += sum_m a[m] * Bs[m*ld + j]   (rows of B broadcast from shared memory)
+template <int K, int NOUT>
+__device__ __forceinline__ void row_gemm_acc(float (&c)[NOUT], const float (&a)[K],
+                                             const float* __restrict__ Bs, int ld) {
+#pragma unroll
+    for (int m = 0; m < K; m++) {
+        float b[NOUT];
+        load_row<NOUT>(b, Bs + m * ld);
+#pragma unroll
+        for (int j = 0; j < NOUT; j++) c[j] = fmaf(a[m], b[j], c[j]);
+    }
+}
+
+// dot of my row with a broadcast vector in shared memory
+template <int K>
+__device__ __forceinline__ float row_dot(const float (&a)[K], const float* __restrict__ v) {
+    float x[K];
+    load_row<K>(x, v);
+    float acc0 = 0.f, acc1 = 0.f;
+#pragma unroll
+    for (int m = 0; m + 1 < K; m += 2) {
+        acc0 = fmaf(a[m], x[m], acc0);
+        acc1 = fmaf(a[m + 1], x[m + 1], acc1);
+    }
+    if (K & 1) acc0 = fmaf(a[K - 1], x[K - 1], acc0);
+    return acc0 + acc1;
+}
+
+// In-place Gauss-Jordan inverse WITHOUT pivoting of a D x D matrix held one row per lane
+// (lane `i` owns row i; lanes i >= D carry zeros and stay harmless).  Same elimination
+// sequence as the reference's invertMatrix on [A | I] (include/utils/matrix.cuh:120-238):
+// the in-place form keeps the evolving inverse column in the slot of the eliminated one.
+// `scratch`: LD floats per knot group, used to broadcast the pivot row.
+template <int D>
+__device__ __forceinline__ void gj_invert_rows(float (&a)[D], int i, float* scratch) {
+#pragma unroll
+    for (int p = 0; p < D; p++) {
+        if (i == p) publish_row<D>(scratch, 0, 0, a);
+        __syncwarp();
+        float rp[D];
+        load_row<D>(rp, scratch);
+        __syncwarp();
+        const float pinv = 1.0f / rp[p];
+        const float f = a[p] * pinv;
+        if (i == p) {
+#pragma unroll
+            for (int j = 0; j < D; j++) a[j] = rp[j] * pinv;
+            a[p] = pinv;
+        } else {
+#pragma unroll
+            for (int j = 0; j < D; j++)
+                if (j != p) a[j] = fmaf(-f, rp[j], a[j]);
+            a[p] = -f;
+        }
+    }
+}
+
+}  // namespace mpcb200
