@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the KKT linear-system hot path (form_schur -> PCG).
+
+Workload (BASELINE.json configs[4] shape, per GPU): `--batch` (4096) independent Kuka IIWA
+64-knot KKT instances ("perturbed start states"), fp32, cold start lambda0 = 0, exit tol 1e-4,
+rho = 1e-3.  A "step" = one fused KKT solve of the whole batch.  Weak scaling: every rank
+owns its own 4096 instances, no data-path collective.
+
+  value     whole-job solves/s with inputs resident in HBM (timed region: per step a D2D
+            restore of G -- the API overwrites it with G^-1 -- a memset of lambda, and the
+            fused kernel; CUDA events, barrier + synchronize on both sides, max over ranks)
+  e2e       same metric through the host-buffer C-ABI solver (pinned host buffers, H2D + D2H
+            inside the timed region)
+  roofline  fused kernel alone: Def. B algorithmic bytes / CUDA-event duration
+            against the measured HBM peak, plus achieved fp32 TFLOP/s (the kernel is
+            FP32/latency bound, not HBM bound -- reported, not hidden)
+  cpu_baseline  the reference's CPU path (oracle Schur restatement + reference QDLDL) on the
+            box's host cores, bounded sample
+  --impl reference   the reference arm: that CPU path with all host threads
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+S, C = 14, 7
+F_SCHUR = 60e3          # flop / knot, reference algorithm
+F_ITER = 2520.0         # flop / knot / PCG iteration
+
+
+def def_b_bytes(N):
+    return 3388 * N - 1596          # SURVEY 8(d) Def. B (fused solve, compulsory I/O)
+
+
+def def_a_bytes(N):
+    return 12908 * N - 1596         # Def. A (S, Pinv materialised)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured"
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True,
+                                     text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4)
+                          if len(r) >= 6 and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def cpu_reference_run(N, sample, steps, warmup, threads):
+    """The reference's CPU implementation of the path on `threads` host threads."""
+    import oracle
+    from mpcgpu_b200 import synth
+    d = synth.gen_kkt_fast(N, sample, seed=synth.BASE_SEED)
+    times = []
+    for it in range(warmup + steps):
+        lam, wall, t_schur, t_qdldl = oracle.cpu_kkt_solve_batch(
+            S, C, N, d["G"], d["C"], d["g"], d["c"], d["rho"], nthreads=threads)
+        if it >= warmup:
+            times.append((wall, t_schur, t_qdldl))
+    wall = float(np.mean([t[0] for t in times]))
+    return {"solves_per_s": sample / wall, "ms_per_step": wall * 1e3,
+            "schur_share": float(np.mean([t[1] / (t[1] + t[2]) for t in times]))}
+
+
+def single_solve_latency(torch, mg, N, tol, reps=200):
+    """Single-instance latency (BASELINE.json metric (i)): PCG-only (cluster kernel vs the
+    reference-style 4-grid-barrier kernel), Schur-only and the fused solve; CUDA events around
+    `reps` back-to-back launches (inputs re-staged by D2D copies outside the kernel but inside
+    the events: negligible, 62 KB)."""
+    from mpcgpu_b200 import synth
+    dev = "cuda"
+    d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + N)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    G0, Cm, g, cv = t(d["G"]), t(d["C"]), t(d["g"]), t(d["c"])
+    z = mg.sizes(S, C, N)
+    Sg = torch.empty((1, z["S"]), device=dev); Pg = torch.empty_like(Sg)
+    gam = torch.empty((1, S * N), device=dev)
+    G = G0.clone()
+    mg.form_schur_system(S, C, N, G, Cm, g, cv, Sg, Pg, gam, d["rho"])
+    lam = torch.zeros((1, S * N), device=dev)
+    it = torch.zeros(1, dtype=torch.int32, device=dev); ex = torch.zeros(1, dtype=torch.uint8, device=dev)
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    ws = torch.empty(2 * S * N + 2 * N + 16, device=dev)
+
+    def timed(fn, reset):
+        for _ in range(10):
+            reset(); fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tot = 0.0
+        for _ in range(reps):
+            reset()
+            e0.record(); fn(); e1.record()
+            e1.synchronize()
+            tot += e0.elapsed_time(e1)
+        return tot / reps * 1e3   # us
+
+    out = {"N": N, "tol": tol}
+    out["pcg_us"] = timed(lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg), lambda: lam.zero_())
+    out["pcg_iters"] = int(it.item())
+    try:
+        out["pcg_refstyle_us"] = timed(lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg, refstyle=True, d_ws=ws),
+                                       lambda: lam.zero_())
+        out["pcg_refstyle_iters"] = int(it.item())
+    except Exception as e:  # cooperative co-residency (N > resident CTAs) can refuse
+        out["pcg_refstyle_us"] = None
+        out["pcg_refstyle_error"] = str(e)[:80]
+    out["schur_us"] = timed(lambda: mg.form_schur_system(S, C, N, G, Cm, g, cv, Sg, Pg, gam, d["rho"]),
+                            lambda: G.copy_(G0))
+    def reset_f():
+        G.copy_(G0); lam.zero_()
+    out["fused_us"] = timed(lambda: mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg), reset_f)
+    out["fused_iters"] = int(it.item())
+    # launch floor: an empty-ish launch of the same geometry = pcg with max_iter 0
+    cfg0 = mg.PcgConfig(pcg_exit_tol=tol, pcg_max_iter=0)
+    out["launch_floor_us"] = timed(lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg0), lambda: None)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--knots", type=int, default=64)
+    ap.add_argument("--tol", type=float, default=1e-4)
+    ap.add_argument("--no-extras", action="store_true")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    N, B = a.knots, a.batch
+    config = {"workload": "%d independent Kuka IIWA (14-state, 7-control) %d-knot KKT instances per GPU, "
+                          "fused Schur formation + PCG (SS preconditioner), cold start, exit tol %g, rho 1e-3"
+                          % (B, N, a.tol),
+              "knot_points": N, "batch_per_gpu": B, "exit_tol": a.tol,
+              "cache": "inputs (%.2f GB per GPU) larger than L2" % (B * def_b_bytes(N) / 1e9)}
+
+    if a.impl == "reference":
+        if rank != 0:
+            return
+        threads = os.cpu_count() or 1
+        sample = max(threads * 8, 256)
+        r = cpu_reference_run(N, sample, a.steps, max(a.warmup, 1), threads)
+        line = {"impl": "reference", "metric": "batched_kkt_solves_per_sec", "value": r["solves_per_s"],
+                "unit": "solves/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": r["solves_per_s"], "unit": "solves/s", "cores": threads, "kind": "reference",
+                                 "sample": "%d of the %d instances per step; Schur formation = oracle restatement "
+                                           "(share %.2f of CPU time), factor/solve = reference QDLDL (oracle/_ref)"
+                                           % (sample, B, r["schur_share"])},
+                "e2e": {"value": r["solves_per_s"], "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+
+    import torch
+    import mpcgpu_b200 as mg
+    from mpcgpu_b200 import synth
+    assert torch.cuda.is_available(), "bench.py needs a GPU (no CPU fallback)"
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    d = synth.gen_kkt_fast(N, B, seed=synth.BASE_SEED + 7919 * rank)
+    pin = lambda x: torch.from_numpy(np.ascontiguousarray(x)).pin_memory()
+    hG, hC, hg, hc = pin(d["G"]), pin(d["C"]), pin(d["g"]), pin(d["c"])
+    G0, Cm, g, cv = hG.to(dev), hC.to(dev), hg.to(dev), hc.to(dev)
+    G = G0.clone()
+    lam = torch.zeros((B, S * N), device=dev)
+    it = torch.zeros(B, dtype=torch.int32, device=dev); ex = torch.ones(B, dtype=torch.uint8, device=dev)
+    cfg = mg.PcgConfig(pcg_exit_tol=a.tol)
+    rho = d["rho"]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(k0=None, k1=None):
+        G.copy_(G0); lam.zero_()
+        if k0 is not None: k0.record()
+        mg.kkt_solve(S, C, N, G, Cm, g, cv, rho, lam, it, ex, cfg, batch=B)
+        if k1 is not None: k1.record()
+
+    for _ in range(max(a.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler: sampler.start()
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = mg.launch_count()
+    barrier()
+    e0.record()
+    for k in range(a.steps):
+        step(*kev[k])
+    e1.record()
+    barrier()
+    launches = mg.launch_count() - n0
+    total_ms = e0.elapsed_time(e1)
+    kern_ms = float(np.mean([x.elapsed_time(y) for x, y in kev]))
+    if dist is not None:
+        tt = torch.tensor([total_ms, kern_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        total_ms, kern_ms = float(tt[0]), float(tt[1])
+    iters = it.cpu().numpy().astype(np.float64)
+    assert int(ex.sum().item()) == 0, "PCG hit max_iter in the bench workload"
+
+    # ---- e2e through the host-buffer C-ABI solver ------------------------------------------
+    hs = mg.HostSolver(S, C, N, B, device=local)
+    hl = torch.zeros((B, S * N)).pin_memory()
+    hi = torch.zeros(B, dtype=torch.int32).pin_memory(); he = torch.ones(B, dtype=torch.uint8).pin_memory()
+    for _ in range(2):
+        hl.zero_(); hs.solve(hG, hC, hg, hc, rho, hl, hi, he, cfg, B)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        hl.zero_()
+        hs.solve(hG, hC, hg, hc, rho, hl, hi, he, cfg, B)
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / a.steps
+    if dist is not None:
+        tt = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_s = float(tt[0])
+    clocks = sampler.stop() if sampler else None
+    assert torch.equal(hl.to(dev), lam), "host path and device path disagree"
+    h2d = 4 * B * (hG[0].numel() + hC[0].numel() + hg[0].numel() + hc[0].numel() + S * N)
+    d2h = B * (4 * S * N + 4 + 1)
+    hs.close()
+
+    if rank == 0:
+        peak, how = load_peaks()
+        ms_per_step = total_ms / a.steps
+        ach = B * def_b_bytes(N) / (kern_ms * 1e-3) / 1e9
+        flops = N * (F_SCHUR * B + F_ITER * iters.sum())
+        prof = os.path.join(ROOT, "profiles", "traffic.json")
+        traffic = json.load(open(prof)).get("fused_kernel_dram_bytes_per_launch") if os.path.exists(prof) else None
+        line = {"metric": "batched_kkt_solves_per_sec", "value": world * B / (ms_per_step * 1e-3), "unit": "solves/s",
+                "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_per_step,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(launches),
+                "pcg_iters": {"mean": float(iters.mean()), "min": int(iters.min()), "max": int(iters.max())},
+                "e2e": {"value": world * B / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
+                        "d2h_bytes_per_step": int(d2h)},
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                             "traffic": traffic, "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs)" if how == "measured" else how,
+                             "kernel": "fused_kernel (schur_rows + pcg_rows)", "kernel_ms": kern_ms,
+                             "bytes_def": "Def. B 3388N-1596 B/instance (SURVEY 8d)",
+                             "def_a_equiv_GBps": B * def_a_bytes(N) / (kern_ms * 1e-3) / 1e9,
+                             "fp32_tflops": flops / (kern_ms * 1e-3) / 1e12,
+                             "note": "FP32/latency bound by design: arithmetic intensity >= 10 flop/B at 0 iterations"}}
+        if world == 1:
+            threads = os.cpu_count() or 1
+            sample = max(threads * 8, 256)
+            r = cpu_reference_run(N, sample, 3, 1, threads)
+            line["cpu_baseline"] = {"value": r["solves_per_s"], "unit": "solves/s", "cores": threads, "kind": "reference",
+                                    "sample": "%d instances x 3 passes; oracle Schur restatement (share %.2f) + reference QDLDL"
+                                              % (sample, r["schur_share"])}
+            if not a.no_extras:
+                line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
+        print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -92,8 +92,9 @@ def bdmv(s, N, M, x):
     return y
 
 
-def pcg(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32):
-    """Returns (lambda, iters, max_iter_exit)."""
+def pcg(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32, mode=0):
+    """Returns (lambda, iters, max_iter_exit).  mode=1: alternate (equally legitimate)
+    floating-point evaluation order, used to measure the fp32 parity noise floor."""
     suf, ct = _dt(dtype)
     S = np.ascontiguousarray(S, dtype=dtype)
     Pinv = np.ascontiguousarray(Pinv, dtype=dtype)
@@ -101,11 +102,24 @@ def pcg(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32):
     lam = np.array(lambda0, dtype=dtype, copy=True)
     iters = ctypes.c_uint(0)
     flag = ctypes.c_ubyte(0)
-    fn = getattr(_lib("oracle"), "oracle_pcg_" + suf)
+    fn = getattr(_lib("oracle"), "oracle_pcg_mode_" + suf)
     fn.restype = None
     fn(ctypes.c_int(s), ctypes.c_int(N), _p(S), _p(Pinv), _p(gamma), _p(lam),
-       ctypes.c_uint(max_iter), ct(exit_tol), ctypes.byref(iters), ctypes.byref(flag))
+       ctypes.c_uint(max_iter), ct(exit_tol), ctypes.byref(iters), ctypes.byref(flag),
+       ctypes.c_int(mode))
     return lam, int(iters.value), bool(flag.value)
+
+
+def pcg_noise_floor(s, N, S32, P32, g32, lambda0, iters):
+    """How far correct fp32 implementations of the SAME `iters` PCG iterations drift apart on
+    this input: max of (plain-order fp32 vs alternate-order fp32) and (fp32 vs fp64), relative
+    to ||lambda||.  The fp64 run uses the identical fp32 inputs and iteration count."""
+    a, _, _ = pcg(s, N, S32, P32, g32, lambda0, iters, 0.0, np.float32, mode=0)
+    b, _, _ = pcg(s, N, S32, P32, g32, lambda0, iters, 0.0, np.float32, mode=1)
+    c, _, _ = pcg(s, N, np.asarray(S32, np.float64), np.asarray(P32, np.float64),
+                  np.asarray(g32, np.float64), lambda0, iters, 0.0, np.float64, mode=0)
+    nrm = max(np.linalg.norm(c), 1e-300)
+    return max(np.linalg.norm(a - b), np.linalg.norm(a - c), np.linalg.norm(b - c)) / nrm
 
 
 def csc_pattern(s, N):

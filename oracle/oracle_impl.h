@@ -239,34 +239,94 @@ static REAL F(dot)(size_t n, const REAL *a, const REAL *b)
  *   max_iter_exit = 1 when the loop ran out of iterations,
  *   exit test: |r . Pinv r| < exit_tol  (ABSOLUTE, on the stored-sign system).
  * ------------------------------------------------------------------------- */
+/* Alternate (equally legitimate) fp evaluation order: block products accumulated
+ * diag -> left -> right with two interleaved partial sums, dot products as per-knot
+ * partial sums reduced by a pairwise tree (the shape of a GPU reduction).  Used by the
+ * tests to MEASURE how far two correct fp32 implementations of the same iteration drift
+ * apart on a given input (the parity noise floor). */
+static void F(bdmv_alt)(int s, int N, const REAL *M, const REAL *x, REAL *y)
+{
+    int k, i, j;
+    const int ss = s * s;
+    for (k = 0; k < N; k++) {
+        const REAL *L = M + ((size_t)k * 3 + 0) * ss;
+        const REAL *D = M + ((size_t)k * 3 + 1) * ss;
+        const REAL *R = M + ((size_t)k * 3 + 2) * ss;
+        for (i = 0; i < s; i++) {
+            REAL a0 = (REAL)0, a1 = (REAL)0, b0 = (REAL)0, b1 = (REAL)0, c0 = (REAL)0, c1 = (REAL)0;
+            for (j = 0; j + 1 < s; j += 2) { a0 += D[i + j * s] * x[(size_t)k * s + j]; a1 += D[i + (j + 1) * s] * x[(size_t)k * s + j + 1]; }
+            if (s & 1) a0 += D[i + (s - 1) * s] * x[(size_t)k * s + s - 1];
+            if (k > 0) {
+                for (j = 0; j + 1 < s; j += 2) { b0 += L[i + j * s] * x[(size_t)(k - 1) * s + j]; b1 += L[i + (j + 1) * s] * x[(size_t)(k - 1) * s + j + 1]; }
+                if (s & 1) b0 += L[i + (s - 1) * s] * x[(size_t)(k - 1) * s + s - 1];
+            }
+            if (k < N - 1) {
+                for (j = 0; j + 1 < s; j += 2) { c0 += R[i + j * s] * x[(size_t)(k + 1) * s + j]; c1 += R[i + (j + 1) * s] * x[(size_t)(k + 1) * s + j + 1]; }
+                if (s & 1) c0 += R[i + (s - 1) * s] * x[(size_t)(k + 1) * s + s - 1];
+            }
+            y[(size_t)k * s + i] = ((b0 + b1) + (a0 + a1)) + (c0 + c1);
+        }
+    }
+}
+
+static REAL F(dot_alt)(int s, int N, const REAL *a, const REAL *b, REAL *work)
+{
+    int k, i, n = N;
+    for (k = 0; k < N; k++) {
+        REAL acc = (REAL)0;
+        for (i = 0; i < s; i++) acc += a[(size_t)k * s + i] * b[(size_t)k * s + i];
+        work[k] = acc;
+    }
+    while (n > 1) {
+        int half = (n + 1) / 2;
+        for (k = 0; k + half < n; k++) work[k] += work[k + half];
+        n = half;
+    }
+    return work[0];
+}
+
+void F(oracle_pcg_mode)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,
+                        REAL *lambda, unsigned max_iter, REAL exit_tol,
+                        unsigned *iters_out, unsigned char *max_iter_exit_out, int mode);
+
 void F(oracle_pcg)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,
                    REAL *lambda, unsigned max_iter, REAL exit_tol,
                    unsigned *iters_out, unsigned char *max_iter_exit_out)
 {
+    F(oracle_pcg_mode)(s, N, S, Pinv, gamma, lambda, max_iter, exit_tol, iters_out,
+                       max_iter_exit_out, 0);
+}
+
+void F(oracle_pcg_mode)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,
+                        REAL *lambda, unsigned max_iter, REAL exit_tol,
+                        unsigned *iters_out, unsigned char *max_iter_exit_out, int mode)
+{
+#define BDMV(M, x, y) do { if (mode) F(bdmv_alt)(s, N, M, x, y); else F(oracle_bdmv)(s, N, M, x, y); } while (0)
+#define DOT(a, b) (mode ? F(dot_alt)(s, N, a, b, work) : F(dot)(n, a, b))
     const size_t n = (size_t)s * N;
-    REAL *r = (REAL *)malloc(sizeof(REAL) * n * 4);
-    REAL *p = r + n, *ups = p + n, *rt = ups + n;
+    REAL *r = (REAL *)malloc(sizeof(REAL) * (n * 4 + N));
+    REAL *p = r + n, *ups = p + n, *rt = ups + n, *work = rt + n;
     REAL eta, eta_new, alpha, beta, v;
     unsigned iter = 0;
     unsigned char max_iter_exit = 1;
     size_t i;
 
-    F(oracle_bdmv)(s, N, S, lambda, ups);
+    BDMV(S, lambda, ups);
     for (i = 0; i < n; i++) r[i] = gamma[i] - ups[i];
-    F(oracle_bdmv)(s, N, Pinv, r, rt);
+    BDMV(Pinv, r, rt);
     for (i = 0; i < n; i++) p[i] = rt[i];
-    eta = F(dot)(n, r, rt);
+    eta = DOT(r, rt);
 
     /* upstream enters the loop unconditionally; an already-converged warm start
      * still costs one iteration unless eta is exactly 0 (guard against 0/0). */
     for (iter = 0; iter < max_iter; iter++) {
-        F(oracle_bdmv)(s, N, S, p, ups);
-        v = F(dot)(n, p, ups);
+        BDMV(S, p, ups);
+        v = DOT(p, ups);
         if (v == (REAL)0) { max_iter_exit = 0; break; }
         alpha = eta / v;
         for (i = 0; i < n; i++) { lambda[i] += alpha * p[i]; r[i] -= alpha * ups[i]; }
-        F(oracle_bdmv)(s, N, Pinv, r, rt);
-        eta_new = F(dot)(n, r, rt);
+        BDMV(Pinv, r, rt);
+        eta_new = DOT(r, rt);
         if (FABS(eta_new) < exit_tol) { iter++; max_iter_exit = 0; break; }
         beta = eta_new / eta;
         eta = eta_new;
@@ -275,6 +335,8 @@ void F(oracle_pcg)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *ga
     *iters_out = iter;
     *max_iter_exit_out = max_iter_exit;
     free(r);
+#undef BDMV
+#undef DOT
 }
 
 /* ---------------------------------------------------------------------------
