@@ -50,16 +50,18 @@ def build(force=False, verbose=False):
     f64 = os.path.join(REFOUT, "libqdldl_f64.so")
     base = os.path.join(REFOUT, "libcpu_baseline.so")
     if have_ref:
+        # qdldl_types.h / qdldl_version.h are cmake-generated in the reference
+        # (qdldl/configure/*.in); oracle/qdldl_cfg holds the two configurations we build.
+        cfg = os.path.join(HERE, "qdldl_cfg")
+        i32 = ["-I", os.path.join(cfg, "f32"), "-I", cfg, "-I", qinc]
+        i64 = ["-I", os.path.join(cfg, "f64"), "-I", cfg, "-I", qinc]
         if force or _stale(f32, [qsrc]):
-            _run(["gcc", "-O3", "-fPIC", "-shared", "-I", qinc, "-o", f32, qsrc])
-        if force or _stale(f64, [qsrc, os.path.join(HERE, "qdldl_f64_types.h")]):
-            # the in-tree qdldl_types.h is the float build; skip it through its include
-            # guard and force-include the double typedefs instead
-            _run(["gcc", "-O3", "-fPIC", "-shared", "-DQDLDL_TYPES_H", "-include",
-                  os.path.join(HERE, "qdldl_f64_types.h"), "-I", qinc, "-o", f64, qsrc])
+            _run(["gcc", "-O3", "-fPIC", "-shared", *i32, "-o", f32, qsrc])
+        if force or _stale(f64, [qsrc]):
+            _run(["gcc", "-O3", "-fPIC", "-shared", *i64, "-o", f64, qsrc])
         if force or _stale(base, own + [qsrc, os.path.join(HERE, "cpu_baseline.c")]):
             _run(["gcc", "-O3", "-ffp-contract=off", "-fPIC", "-shared", "-pthread",
-                  "-I", qinc, "-o", base, "cpu_baseline.c", "mpc_oracle.c", qsrc, "-lm"])
+                  *i32, "-o", base, "cpu_baseline.c", "mpc_oracle.c", qsrc, "-lm"])
         if verbose:
             print("built", f32, f64, base)
     else:
