@@ -63,27 +63,27 @@ cudaError_t launch(const BatchArgs& a, cudaStream_t st) {
     return e;
 }
 
-// (KPC, CL) tiling: N <= KPC*CL.  MPCGPU_B200_KPC=16 selects the low-latency tiling
-// (half the knots per CTA, twice the cluster) where it exists.
+// (KPC, CL) tiling: N <= KPC*CL.  Default: 64 knots per CTA (a 64-knot instance lives in one
+// SM, no cluster barrier at all).  MPCGPU_B200_KPC=32 selects half the knots per CTA and
+// twice the cluster (more SMs per instance) for experiments on single-solve latency.
 template <int KIND>
 cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
     static const int pref_kpc = [] {
         const char* e = getenv("MPCGPU_B200_KPC");
-        return e ? atoi(e) : 32;
+        return e ? atoi(e) : 64;
     }();
     const int N = a.N;
-    if (pref_kpc == 16) {
-        if (N <= 16) return launch<Cfg<14, 7, 16, 1>, KIND>(a, st);
-        if (N <= 32) return launch<Cfg<14, 7, 16, 2>, KIND>(a, st);
-        if (N <= 64) return launch<Cfg<14, 7, 16, 4>, KIND>(a, st);
-        if (N <= 128) return launch<Cfg<14, 7, 16, 8>, KIND>(a, st);
-        if (N <= 256) return launch<Cfg<14, 7, 16, 16>, KIND>(a, st);
+    if (N <= 16) return launch<Cfg<16, 1>, KIND>(a, st);
+    if (N <= 32) return launch<Cfg<32, 1>, KIND>(a, st);
+    if (pref_kpc == 32) {
+        if (N <= 64) return launch<Cfg<32, 2>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<32, 4>, KIND>(a, st);
+        if (N <= 256) return launch<Cfg<32, 8>, KIND>(a, st);
     }
-    if (N <= 32) return launch<Cfg<14, 7, 32, 1>, KIND>(a, st);
-    if (N <= 64) return launch<Cfg<14, 7, 32, 2>, KIND>(a, st);
-    if (N <= 128) return launch<Cfg<14, 7, 32, 4>, KIND>(a, st);
-    if (N <= 256) return launch<Cfg<14, 7, 32, 8>, KIND>(a, st);
-    if (N <= 512) return launch<Cfg<14, 7, 32, 16>, KIND>(a, st);
+    if (N <= 64) return launch<Cfg<64, 1>, KIND>(a, st);
+    if (N <= 128) return launch<Cfg<64, 2>, KIND>(a, st);
+    if (N <= 256) return launch<Cfg<64, 4>, KIND>(a, st);
+    if (N <= 512) return launch<Cfg<64, 8>, KIND>(a, st);
     return cudaErrorInvalidValue;
 }
 

@@ -1,7 +1,7 @@
 // kernels.cuh -- __global__ entry points built from kkt_device.cuh.
 //
 // Grid: batch * CL CTAs, one thread-block cluster of CL CTAs per KKT instance, KPC knots per
-// CTA, 16 lanes per knot.  Instance b's buffers start at base + b * <elements per instance>
+// CTA, 8 lanes per knot.  Instance b's buffers start at base + b * <elements per instance>
 // (the reference's single-instance buffers, concatenated).
 #pragma once
 #include "kkt_device.cuh"
@@ -21,69 +21,97 @@ struct BatchArgs {
     unsigned* iters; uint8_t* exits;
 };
 
-// store my rows to the reference [N][3][S*S] column-major layout (store_block_bd semantics,
-// include/pcg/linsys_setup_no_precond.cuh:29-38); corner blocks are written as zeros.
+// PROW column offset of block column `blk` (0 left, 1 diag, 2 right) of the reference layout
 template <class CF>
-__device__ __forceinline__ void store_rows(const Rows<CF::S>& R, float* Sg, float* Pg, float* gam,
-                                           int N) {
-    constexpr int S = CF::S, SS = S * S;
-    const int g = threadIdx.x / LPK, i = threadIdx.x % LPK;
-    const int k = cluster_rank<CF::CL>() * CF::KPC + g;
-    if (k >= N || i >= S) return;
-    float* s0 = Sg + (size_t)k * 3 * SS + i;
-    float* p0 = Pg + (size_t)k * 3 * SS + i;
+__device__ __forceinline__ int prow_col(int blk) { return blk == 1 ? CF::cD : (blk == 0 ? CF::cL : CF::cR); }
+
+// store to the reference [N][3][S*S] column-major layout (store_block_bd semantics,
+// include/pcg/linsys_setup_no_precond.cuh:29-38); corner blocks are written as zeros.
+// S rows come from registers, Pinv rows from shared memory (coalesced).
+template <class CF>
+__device__ __forceinline__ void store_rows(const float* smem, const Rows& R, float* Sg, float* Pg,
+                                           float* gam, int N) {
+    constexpr int S = 14, SS = S * S;
+    const int g = threadIdx.x >> 3, t = threadIdx.x & 7;
+    const int k0 = cluster_rank<CF::CL>() * CF::KPC;
+    const int k = k0 + g;
+    if (k < N && t < 7) {
+        const int r0 = t, r1 = t + 7;
+        float* s0 = Sg + (size_t)k * 3 * SS;
 #pragma unroll
-    for (int j = 0; j < S; j++) {
-        s0[0 * SS + j * S] = R.Sl[j]; s0[1 * SS + j * S] = R.Sd[j]; s0[2 * SS + j * S] = R.Sr[j];
-        p0[0 * SS + j * S] = R.Pl[j]; p0[1 * SS + j * S] = R.Pd[j]; p0[2 * SS + j * S] = R.Pr[j];
+        for (int j = 0; j < S; j++) {
+            s0[0 * SS + j * S + r0] = getp(R.Sl[0], j); s0[0 * SS + j * S + r1] = getp(R.Sl[1], j);
+            s0[1 * SS + j * S + r0] = getp(R.Sd[0], j); s0[1 * SS + j * S + r1] = getp(R.Sd[1], j);
+            s0[2 * SS + j * S + r0] = getp(R.Sr[0], j); s0[2 * SS + j * S + r1] = getp(R.Sr[1], j);
+        }
+        gam[(size_t)k * S + r0] = R.gamma[0];
+        gam[(size_t)k * S + r1] = R.gamma[1];
     }
-    gam[(size_t)k * S + i] = R.gamma;
+    const int nk = min(CF::KPC, N - k0);
+    for (int e = threadIdx.x; e < nk * 3 * SS; e += CF::NT) {
+        const int gg = e / (3 * SS), w = e - gg * 3 * SS;
+        const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
+        Pg[(size_t)(k0 + gg) * 3 * SS + w] = smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j];
+    }
 }
 
-// load my rows from the reference layout (load_block_bd semantics); the never-written corner
-// blocks S[0][0], S[N-1][2], Pinv[0][0], Pinv[N-1][2] are NOT read.
+// load from the reference layout (load_block_bd semantics); the never-written corner blocks
+// S[0][0], S[N-1][2], Pinv[0][0], Pinv[N-1][2] are NOT read.
 template <class CF>
-__device__ __forceinline__ void load_rows(Rows<CF::S>& R, const float* __restrict__ Sg,
+__device__ __forceinline__ void load_rows(float* smem, Rows& R, const float* __restrict__ Sg,
                                           const float* __restrict__ Pg,
                                           const float* __restrict__ gam, int N) {
-    constexpr int S = CF::S, SS = S * S;
-    const int g = threadIdx.x / LPK, i = threadIdx.x % LPK;
-    const int k = cluster_rank<CF::CL>() * CF::KPC + g;
-    const bool on = (k < N) && (i < S);
+    constexpr int S = 14, SS = S * S;
+    const int g = threadIdx.x >> 3, t = threadIdx.x & 7;
+    const int k0 = cluster_rank<CF::CL>() * CF::KPC;
+    const int k = k0 + g;
+    const bool on = (k < N) && (t < 7);
+    const int r0 = on ? t : 0, r1 = r0 + 7;
     const bool hl = on && k > 0, hr = on && (k + 1 < N);
-    const float* s0 = Sg + (size_t)k * 3 * SS + i;
-    const float* p0 = Pg + (size_t)k * 3 * SS + i;
+    const float* s0 = Sg + (size_t)k * 3 * SS;
 #pragma unroll
     for (int j = 0; j < S; j++) {
-        R.Sl[j] = hl ? __ldg(s0 + 0 * SS + j * S) : 0.f;
-        R.Sd[j] = on ? __ldg(s0 + 1 * SS + j * S) : 0.f;
-        R.Sr[j] = hr ? __ldg(s0 + 2 * SS + j * S) : 0.f;
-        R.Pl[j] = hl ? __ldg(p0 + 0 * SS + j * S) : 0.f;
-        R.Pd[j] = on ? __ldg(p0 + 1 * SS + j * S) : 0.f;
-        R.Pr[j] = hr ? __ldg(p0 + 2 * SS + j * S) : 0.f;
+        setp(R.Sl[0], j, hl ? __ldg(s0 + 0 * SS + j * S + r0) : 0.f); setp(R.Sl[1], j, hl ? __ldg(s0 + 0 * SS + j * S + r1) : 0.f);
+        setp(R.Sd[0], j, on ? __ldg(s0 + 1 * SS + j * S + r0) : 0.f); setp(R.Sd[1], j, on ? __ldg(s0 + 1 * SS + j * S + r1) : 0.f);
+        setp(R.Sr[0], j, hr ? __ldg(s0 + 2 * SS + j * S + r0) : 0.f); setp(R.Sr[1], j, hr ? __ldg(s0 + 2 * SS + j * S + r1) : 0.f);
     }
-    R.gamma = on ? __ldg(gam + (size_t)k * S + i) : 0.f;
+    R.gamma[0] = on ? __ldg(gam + (size_t)k * S + r0) : 0.f;
+    R.gamma[1] = on ? __ldg(gam + (size_t)k * S + r1) : 0.f;
+    for (int e = threadIdx.x; e < CF::KPC * 3 * SS; e += CF::NT) {
+        const int gg = e / (3 * SS), w = e - gg * 3 * SS;
+        const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
+        const int kk = k0 + gg;
+        const bool corner = (kk == 0 && blk == 0) || (kk == N - 1 && blk == 2);
+        float v = 0.f;
+        if (kk < N && !corner) v = __ldg(Pg + (size_t)kk * 3 * SS + w);
+        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j] = v;
+    }
+    for (int e = threadIdx.x; e < CF::KPC * S; e += CF::NT) {      // row padding (never used in sums)
+        const int gg = e / S, i = e - gg * S;
+        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + 42] = 0.f;
+        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + 43] = 0.f;
+    }
+    __syncthreads();
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, 1) schur_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, 512 / CF::NT) schur_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int b = blockIdx.x / CF::CL;
     KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
-    Rows<CF::S> R;
+    Rows R;
     schur_rows<CF>(smem, P, a.N, a.rho, R);
-    store_rows<CF>(R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
-    if (CF::CL > 1) cluster_sync_all<CF::CL>();
+    store_rows<CF>(smem, R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, 1) pcg_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, 512 / CF::NT) pcg_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int b = blockIdx.x / CF::CL;
-    Rows<CF::S> R;
-    load_rows<CF>(R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
+    Rows R;
+    load_rows<CF>(smem, R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
 }
@@ -91,12 +119,12 @@ __global__ void __launch_bounds__(CF::NT, 1) pcg_kernel(BatchArgs a) {
 // fused KKT solve: S and Pinv never leave the SM (Def. B traffic: read G,C,g,c,lambda0;
 // write lambda, G^-1).
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, 1) fused_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, 512 / CF::NT) fused_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int b = blockIdx.x / CF::CL;
     KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
-    Rows<CF::S> R;
+    Rows R;
     schur_rows<CF>(smem, P, a.N, a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
