@@ -63,27 +63,42 @@ cudaError_t launch(const BatchArgs& a, cudaStream_t st) {
     return e;
 }
 
-// (KPC, CL) tiling: N <= KPC*CL.  Default: 64 knots per CTA (a 64-knot instance lives in one
-// SM, no cluster barrier at all).  MPCGPU_B200_KPC=32 selects half the knots per CTA and
-// twice the cluster (more SMs per instance) for experiments on single-solve latency.
+// (KPC, CL, LPK) tiling: N <= KPC*CL.  Default: 64 knots per CTA, 4 lanes per knot (a 64-knot
+// instance lives in one SM with 256 threads, no cluster barrier at all).  The environment
+// variable MPCGPU_B200_TILING=<kpc>x<lpk> (e.g. 32x8) selects other tilings for experiments.
 template <int KIND>
 cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
-    static const int pref_kpc = [] {
-        const char* e = getenv("MPCGPU_B200_KPC");
-        return e ? atoi(e) : 64;
+    static const int pref = [] {
+        const char* e = getenv("MPCGPU_B200_TILING");
+        int kpc = 64, lpk = 4;
+        if (e && sscanf(e, "%dx%d", &kpc, &lpk) != 2) { kpc = 64; lpk = 4; }
+        return kpc * 100 + lpk;
     }();
     const int N = a.N;
-    if (N <= 16) return launch<Cfg<16, 1>, KIND>(a, st);
-    if (N <= 32) return launch<Cfg<32, 1>, KIND>(a, st);
-    if (pref_kpc == 32) {
-        if (N <= 64) return launch<Cfg<32, 2>, KIND>(a, st);
-        if (N <= 128) return launch<Cfg<32, 4>, KIND>(a, st);
-        if (N <= 256) return launch<Cfg<32, 8>, KIND>(a, st);
+    if (pref == 6408) {
+        if (N <= 64) return launch<Cfg<64, 1, 8>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<64, 2, 8>, KIND>(a, st);
+        if (N <= 256) return launch<Cfg<64, 4, 8>, KIND>(a, st);
+        if (N <= 512) return launch<Cfg<64, 8, 8>, KIND>(a, st);
     }
-    if (N <= 64) return launch<Cfg<64, 1>, KIND>(a, st);
-    if (N <= 128) return launch<Cfg<64, 2>, KIND>(a, st);
-    if (N <= 256) return launch<Cfg<64, 4>, KIND>(a, st);
-    if (N <= 512) return launch<Cfg<64, 8>, KIND>(a, st);
+    if (pref == 3208) {
+        if (N <= 32) return launch<Cfg<32, 1, 8>, KIND>(a, st);
+        if (N <= 64) return launch<Cfg<32, 2, 8>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<32, 4, 8>, KIND>(a, st);
+        if (N <= 256) return launch<Cfg<32, 8, 8>, KIND>(a, st);
+    }
+    if (pref == 3204) {
+        if (N <= 32) return launch<Cfg<32, 1, 4>, KIND>(a, st);
+        if (N <= 64) return launch<Cfg<32, 2, 4>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<32, 4, 4>, KIND>(a, st);
+        if (N <= 256) return launch<Cfg<32, 8, 4>, KIND>(a, st);
+    }
+    if (N <= 16) return launch<Cfg<16, 1, 8>, KIND>(a, st);
+    if (N <= 32) return launch<Cfg<32, 1, 4>, KIND>(a, st);
+    if (N <= 64) return launch<Cfg<64, 1, 4>, KIND>(a, st);
+    if (N <= 128) return launch<Cfg<64, 2, 4>, KIND>(a, st);
+    if (N <= 256) return launch<Cfg<64, 4, 4>, KIND>(a, st);
+    if (N <= 512) return launch<Cfg<64, 8, 4>, KIND>(a, st);
     return cudaErrorInvalidValue;
 }
 

@@ -1,7 +1,7 @@
 // kernels.cuh -- __global__ entry points built from kkt_device.cuh.
 //
 // Grid: batch * CL CTAs, one thread-block cluster of CL CTAs per KKT instance, KPC knots per
-// CTA, 8 lanes per knot.  Instance b's buffers start at base + b * <elements per instance>
+// CTA, LPK lanes per knot.  Instance b's buffers start at base + b * <elements per instance>
 // (the reference's single-instance buffers, concatenated).
 #pragma once
 #include "kkt_device.cuh"
@@ -29,23 +29,27 @@ __device__ __forceinline__ int prow_col(int blk) { return blk == 1 ? CF::cD : (b
 // include/pcg/linsys_setup_no_precond.cuh:29-38); corner blocks are written as zeros.
 // S rows come from registers, Pinv rows from shared memory (coalesced).
 template <class CF>
-__device__ __forceinline__ void store_rows(const float* smem, const Rows& R, float* Sg, float* Pg,
-                                           float* gam, int N) {
+__device__ __forceinline__ void store_rows(const float* smem, const Rows<CF::RPT>& R, float* Sg,
+                                           float* Pg, float* gam, int N) {
     constexpr int S = 14, SS = S * S;
-    const int g = threadIdx.x >> 3, t = threadIdx.x & 7;
+    const int g = threadIdx.x / CF::LPK, t = threadIdx.x % CF::LPK;
     const int k0 = cluster_rank<CF::CL>() * CF::KPC;
     const int k = k0 + g;
-    if (k < N && t < 7) {
-        const int r0 = t, r1 = t + 7;
+    const RowMap<CF::LPK, CF::RPT, 14> rm(t);
+    if (k < N) {
         float* s0 = Sg + (size_t)k * 3 * SS;
 #pragma unroll
-        for (int j = 0; j < S; j++) {
-            s0[0 * SS + j * S + r0] = getp(R.Sl[0], j); s0[0 * SS + j * S + r1] = getp(R.Sl[1], j);
-            s0[1 * SS + j * S + r0] = getp(R.Sd[0], j); s0[1 * SS + j * S + r1] = getp(R.Sd[1], j);
-            s0[2 * SS + j * S + r0] = getp(R.Sr[0], j); s0[2 * SS + j * S + r1] = getp(R.Sr[1], j);
+        for (int j = 0; j < CF::RPT; j++) {
+            if (!rm.ok[j]) continue;
+            const int r = rm.row[j];
+#pragma unroll
+            for (int c = 0; c < S; c++) {
+                s0[0 * SS + c * S + r] = getp(R.Sl[j], c);
+                s0[1 * SS + c * S + r] = getp(R.Sd[j], c);
+                s0[2 * SS + c * S + r] = getp(R.Sr[j], c);
+            }
+            gam[(size_t)k * S + r] = R.gamma[j];
         }
-        gam[(size_t)k * S + r0] = R.gamma[0];
-        gam[(size_t)k * S + r1] = R.gamma[1];
     }
     const int nk = min(CF::KPC, N - k0);
     for (int e = threadIdx.x; e < nk * 3 * SS; e += CF::NT) {
@@ -58,25 +62,28 @@ __device__ __forceinline__ void store_rows(const float* smem, const Rows& R, flo
 // load from the reference layout (load_block_bd semantics); the never-written corner blocks
 // S[0][0], S[N-1][2], Pinv[0][0], Pinv[N-1][2] are NOT read.
 template <class CF>
-__device__ __forceinline__ void load_rows(float* smem, Rows& R, const float* __restrict__ Sg,
+__device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const float* __restrict__ Sg,
                                           const float* __restrict__ Pg,
                                           const float* __restrict__ gam, int N) {
     constexpr int S = 14, SS = S * S;
-    const int g = threadIdx.x >> 3, t = threadIdx.x & 7;
+    const int g = threadIdx.x / CF::LPK, t = threadIdx.x % CF::LPK;
     const int k0 = cluster_rank<CF::CL>() * CF::KPC;
     const int k = k0 + g;
-    const bool on = (k < N) && (t < 7);
-    const int r0 = on ? t : 0, r1 = r0 + 7;
-    const bool hl = on && k > 0, hr = on && (k + 1 < N);
+    const RowMap<CF::LPK, CF::RPT, 14> rm(t);
     const float* s0 = Sg + (size_t)k * 3 * SS;
 #pragma unroll
-    for (int j = 0; j < S; j++) {
-        setp(R.Sl[0], j, hl ? __ldg(s0 + 0 * SS + j * S + r0) : 0.f); setp(R.Sl[1], j, hl ? __ldg(s0 + 0 * SS + j * S + r1) : 0.f);
-        setp(R.Sd[0], j, on ? __ldg(s0 + 1 * SS + j * S + r0) : 0.f); setp(R.Sd[1], j, on ? __ldg(s0 + 1 * SS + j * S + r1) : 0.f);
-        setp(R.Sr[0], j, hr ? __ldg(s0 + 2 * SS + j * S + r0) : 0.f); setp(R.Sr[1], j, hr ? __ldg(s0 + 2 * SS + j * S + r1) : 0.f);
+    for (int j = 0; j < CF::RPT; j++) {
+        const bool on = (k < N) && rm.ok[j];
+        const bool hl = on && k > 0, hr = on && (k + 1 < N);
+        const int r = rm.row[j];
+#pragma unroll
+        for (int c = 0; c < S; c++) {
+            setp(R.Sl[j], c, hl ? __ldg(s0 + 0 * SS + c * S + r) : 0.f);
+            setp(R.Sd[j], c, on ? __ldg(s0 + 1 * SS + c * S + r) : 0.f);
+            setp(R.Sr[j], c, hr ? __ldg(s0 + 2 * SS + c * S + r) : 0.f);
+        }
+        R.gamma[j] = on ? __ldg(gam + (size_t)k * S + r) : 0.f;
     }
-    R.gamma[0] = on ? __ldg(gam + (size_t)k * S + r0) : 0.f;
-    R.gamma[1] = on ? __ldg(gam + (size_t)k * S + r1) : 0.f;
     for (int e = threadIdx.x; e < CF::KPC * 3 * SS; e += CF::NT) {
         const int gg = e / (3 * SS), w = e - gg * 3 * SS;
         const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
@@ -95,22 +102,22 @@ __device__ __forceinline__ void load_rows(float* smem, Rows& R, const float* __r
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, 512 / CF::NT) schur_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) schur_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int b = blockIdx.x / CF::CL;
     KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
-    Rows R;
+    Rows<CF::RPT> R;
     schur_rows<CF>(smem, P, a.N, a.rho, R);
     store_rows<CF>(smem, R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, 512 / CF::NT) pcg_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int b = blockIdx.x / CF::CL;
-    Rows R;
+    Rows<CF::RPT> R;
     load_rows<CF>(smem, R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
@@ -119,12 +126,12 @@ __global__ void __launch_bounds__(CF::NT, 512 / CF::NT) pcg_kernel(BatchArgs a) 
 // fused KKT solve: S and Pinv never leave the SM (Def. B traffic: read G,C,g,c,lambda0;
 // write lambda, G^-1).
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, 512 / CF::NT) fused_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int b = blockIdx.x / CF::CL;
     KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
-    Rows R;
+    Rows<CF::RPT> R;
     schur_rows<CF>(smem, P, a.N, a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);

@@ -8,33 +8,38 @@
 //   phase 2  include/pcg/linsys_setup.cuh:9-137     (SS preconditioner off-diagonals)
 //   PCG      GBD-PCG gpu_pcg.cuh (absent; call site include/pcg/sqp.cuh:142-166,275)
 //
-// Mapping ("row-pair owner"): 8 lanes per knot, lane t < 7 owns rows t and t+7 of every
-// 14 x 14 block of its knot (lane 7 idles: 87.5 % lane use, the same as 14 of 16).  Four knots
-// share a warp, so everything inside a knot synchronises with __syncwarp().  One CTA holds up
-// to 64 knots (512 threads); a whole 64-knot instance lives in ONE SM:
-//   * S block rows (3 x 14 floats per row) stay in registers for the whole solve (84 regs);
+// Mapping ("row owner"): LPK lanes per knot (4 or 8); lane t owns rows t, t+LPK, t+2*LPK, ...
+// (< 14) of every 14 x 14 block of its knot: RPT = 4 or 2 row slots per lane, 14 of 16 slots
+// used.  32/LPK knots share a warp, so everything inside a knot synchronises with
+// __syncwarp().  One CTA holds up to 64 knots; a whole 64-knot instance lives in ONE SM:
+//   * S block rows (3 x 14 floats per row) stay in registers for the whole solve;
 //   * Pinv block rows live in shared memory as PROW[knot][row][44] = [Pd | Pl | Pr | pad2]
-//     (row stride 44 floats: 16 B aligned and bank-conflict free for the 7 active lanes);
+//     (row stride 44 floats, knot stride 624: 16 B aligned and bank-conflict free);
 //   * all pair-wise arithmetic is FFMA2 (fma.rn.f32x2, sm_100): half the FMA issue slots.
+// The PCG iteration is bound by the shared-memory pipe (128 B/clk/SM): every x value a lane
+// needs is one register delivery, every Pinv coefficient read from shared memory is 4 B per
+// FMA.  LPK = 4 (4 rows per lane) halves the x deliveries per FMA relative to LPK = 8.
 // The Schur phase uses the same shared memory as scratch: the Pd columns of PROW first hold
 // Qt^-1 rows, then -theta^-1 rows; the (not yet written) Pl / Pr columns hold B, R^-1 and
 // the knot's vectors; a second tile per knot holds A, then phi.
-// Longer horizons use a thread-block cluster of CL CTAs (64 knots each) with DSMEM halos.
+// Longer horizons use a thread-block cluster of CL CTAs with DSMEM halos.
 #pragma once
 #include "common.cuh"
 
 namespace mpcb200 {
 
-template <int KPC_, int CL_>
+template <int KPC_, int CL_, int LPK_>
 struct Cfg {
-    static constexpr int S = 14, C = 7, H = 7;
+    static constexpr int S = 14, C = 7;
     static constexpr int KPC = KPC_, CL = CL_;
-    static constexpr int LPK = 8;               // lanes per knot
+    static constexpr int LPK = LPK_;            // lanes per knot
+    static constexpr int RPT = (S + LPK - 1) / LPK;   // row slots per lane (14 x 14 blocks)
+    static constexpr int RPT7 = (C + LPK - 1) / LPK;  // row slots per lane (7 x 7 block)
     static constexpr int NT = KPC * LPK;        // threads per CTA
     static constexpr int NW = NT / 32;          // warps per CTA
     static constexpr int SLOTS = KPC + 2;       // one halo knot on both sides
     static constexpr int PR = 44;               // floats per PROW row
-    static constexpr int PK = S * PR;           // floats per PROW knot (616)
+    static constexpr int PK = S * PR + 8;       // floats per PROW knot (624 = 16 mod 32 banks)
     static constexpr int TK = S * S;            // floats per A / phi tile (196)
     static constexpr int VK = 16;               // floats per vector slot
     static constexpr int cD = 0, cL = 14, cR = 28;   // column offsets of Pd | Pl | Pr in a row
@@ -49,7 +54,9 @@ struct Cfg {
     static constexpr int oRed = oHal + 4 * VK;          // [2 bufs][NREDP]
     static constexpr int FLOATS = oRed + 2 * NREDP;
     static constexpr size_t SMEM_BYTES = sizeof(float) * FLOATS;
-    static_assert(KPC % 4 == 0 && KPC <= 128, "whole warps, <= 1024 threads");
+    static constexpr int MIN_CTAS = (LPK == 4) ? 1 : (512 / NT > 0 ? 512 / NT : 1);
+    static_assert(LPK == 4 || LPK == 8, "4 or 8 lanes per knot");
+    static_assert(NT % 32 == 0 && NT <= 1024, "whole warps, <= 1024 threads");
     static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory of sm_100");
 };
 
@@ -61,16 +68,18 @@ struct KktPtrs {
     const float* c;   // constraint residuals
 };
 
-// Register-resident part of a knot's block row pair: rows t and t+7 of the stored (negated)
+// Register-resident part of a knot's block rows: the lane's RPT rows of the stored (negated)
 // Schur complement, as float2 pairs.
+template <int RPT>
 struct Rows {
-    float2 Sl[2][7], Sd[2][7], Sr[2][7];
-    float gamma[2];
+    float2 Sl[RPT][7], Sd[RPT][7], Sr[RPT][7];
+    float gamma[RPT];
 };
 
 // ---- small float2 helpers ----------------------------------------------------------------
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
+__device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
 __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
 __device__ __forceinline__ float getp(const float2 (&a)[7], int i) { return (i & 1) ? a[i >> 1].y : a[i >> 1].x; }
 __device__ __forceinline__ void setp(float2 (&a)[7], int i, float v) { if (i & 1) a[i >> 1].y = v; else a[i >> 1].x = v; }
@@ -108,92 +117,99 @@ __device__ __forceinline__ float2 dot14_acc(const float2 (&a)[7], const float2 (
     for (int q = 0; q < 7; q++) acc = fma2(a[q], x[q], acc);
     return acc;
 }
+__device__ __forceinline__ float hsum(float2 a) { return a.x + a.y; }
 
-// c0 += a0 * b, c1 += a1 * b  (one broadcast row b shared by the thread's two rows)
-__device__ __forceinline__ void axpy2(float2 (&c0)[7], float2 (&c1)[7], float a0, float a1,
-                                      const float2 (&b)[7]) {
-    const float2 s0 = splat(a0), s1 = splat(a1);
+// c[j] += a[j] * b for the lane's RPT rows (one broadcast row b shared by all of them)
+template <int RPT>
+__device__ __forceinline__ void axpy_rows(float2 (&c)[RPT][7], const float (&a)[RPT], const float2 (&b)[7]) {
 #pragma unroll
-    for (int q = 0; q < 7; q++) { c0[q] = fma2(s0, b[q], c0[q]); c1[q] = fma2(s1, b[q], c1[q]); }
+    for (int j = 0; j < RPT; j++) {
+        const float2 s = splat(a[j]);
+#pragma unroll
+        for (int q = 0; q < 7; q++) c[j][q] = fma2(s, b[q], c[j][q]);
+    }
 }
 
-// In-place Gauss-Jordan inverse WITHOUT pivoting of a 14 x 14 matrix held as row pairs (lane t
-// owns rows t and t+7).  Same elimination sequence as the reference's invertMatrix on [A | I]
+// Row bookkeeping of a lane: slot j holds row t + LPK*j (rows >= D do not exist; such slots
+// shadow row 0 for addressing, never store, and carry zeros into every sum).
+template <int LPK, int RPT, int D>
+struct RowMap {
+    int row[RPT];
+    bool ok[RPT];
+    __device__ __forceinline__ RowMap(int t) {
+#pragma unroll
+        for (int j = 0; j < RPT; j++) { const int r = t + LPK * j; ok[j] = r < D; row[j] = ok[j] ? r : 0; }
+    }
+};
+
+// In-place Gauss-Jordan inverse WITHOUT pivoting of a 14 x 14 matrix held as rows (lane t
+// owns rows t + LPK*j).  Same elimination sequence as the reference's invertMatrix on [A | I]
 // (include/utils/matrix.cuh:120-238): the in-place form keeps the evolving inverse column in
 // the slot of the eliminated one.  `piv`: 16 floats of shared memory private to this knot.
-__device__ __forceinline__ void gj14(float2 (&a0)[7], float2 (&a1)[7], int t, bool act, float* piv) {
+template <int LPK, int RPT>
+__device__ __forceinline__ void gj14(float2 (&a)[RPT][7], int t, float* piv) {
 #pragma unroll
     for (int p = 0; p < 14; p++) {
-        const int owner = p % 7;
-        const bool hi = p >= 7;
-        if (act && t == owner) { if (hi) st14_v4(piv, a1); else st14_v4(piv, a0); }
+        const int owner = p % LPK, slot = p / LPK;
+        if (t == owner) st14_v4(piv, a[slot]);
         __syncwarp();
         float2 rp[7];
         ld14_v4(rp, piv);
         __syncwarp();
         const float pinv = 1.0f / getp(rp, p);
-        const bool own0 = !hi && t == owner, own1 = hi && t == owner;
-        {
-            const float f = getp(a0, p) * pinv;
-            if (own0) {
 #pragma unroll
-                for (int q = 0; q < 7; q++) a0[q] = f2(rp[q].x * pinv, rp[q].y * pinv);
-                setp(a0, p, pinv);
+        for (int j = 0; j < RPT; j++) {
+            const float f = getp(a[j], p) * pinv;
+            if (j == slot && t == owner) {
+#pragma unroll
+                for (int q = 0; q < 7; q++) a[j][q] = f2(rp[q].x * pinv, rp[q].y * pinv);
+                setp(a[j], p, pinv);
             } else {
                 const float2 nf = splat(-f);
 #pragma unroll
-                for (int q = 0; q < 7; q++) a0[q] = fma2(nf, rp[q], a0[q]);
-                setp(a0, p, -f);
-            }
-        }
-        {
-            const float f = getp(a1, p) * pinv;
-            if (own1) {
-#pragma unroll
-                for (int q = 0; q < 7; q++) a1[q] = f2(rp[q].x * pinv, rp[q].y * pinv);
-                setp(a1, p, pinv);
-            } else {
-                const float2 nf = splat(-f);
-#pragma unroll
-                for (int q = 0; q < 7; q++) a1[q] = fma2(nf, rp[q], a1[q]);
-                setp(a1, p, -f);
+                for (int q = 0; q < 7; q++) a[j][q] = fma2(nf, rp[q], a[j][q]);
+                setp(a[j], p, -f);
             }
         }
     }
 }
 
-// 7 x 7 Gauss-Jordan, lane t < 7 owns row t (8 floats, last one padding).  piv: 8 floats.
-__device__ __forceinline__ void gj7(float (&a)[8], int t, bool act, float* piv) {
+// 7 x 7 Gauss-Jordan, rows t + LPK*j (8 floats per row, last one padding).  piv: 8 floats.
+template <int LPK, int RPT7>
+__device__ __forceinline__ void gj7(float (&a)[RPT7][8], int t, float* piv) {
 #pragma unroll
     for (int p = 0; p < 7; p++) {
-        if (act && t == p) {
-            reinterpret_cast<float4*>(piv)[0] = make_float4(a[0], a[1], a[2], a[3]);
-            reinterpret_cast<float4*>(piv)[1] = make_float4(a[4], a[5], a[6], 0.f);
+        const int owner = p % LPK, slot = p / LPK;
+        if (t == owner) {
+            reinterpret_cast<float4*>(piv)[0] = make_float4(a[slot][0], a[slot][1], a[slot][2], a[slot][3]);
+            reinterpret_cast<float4*>(piv)[1] = make_float4(a[slot][4], a[slot][5], a[slot][6], 0.f);
         }
         __syncwarp();
         const float4 u = reinterpret_cast<const float4*>(piv)[0], v = reinterpret_cast<const float4*>(piv)[1];
         __syncwarp();
         const float rp[7] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z};
         const float pinv = 1.0f / rp[p];
-        const float f = a[p] * pinv;
-        if (t == p) {
 #pragma unroll
-            for (int j = 0; j < 7; j++) a[j] = rp[j] * pinv;
-            a[p] = pinv;
-        } else {
+        for (int j = 0; j < RPT7; j++) {
+            const float f = a[j][p] * pinv;
+            if (j == slot && t == owner) {
 #pragma unroll
-            for (int j = 0; j < 7; j++)
-                if (j != p) a[j] = fmaf(-f, rp[j], a[j]);
-            a[p] = -f;
+                for (int c = 0; c < 7; c++) a[j][c] = rp[c] * pinv;
+                a[j][p] = pinv;
+            } else {
+#pragma unroll
+                for (int c = 0; c < 7; c++)
+                    if (c != p) a[j][c] = fmaf(-f, rp[c], a[j][c]);
+                a[j][p] = -f;
+            }
         }
     }
 }
 
 // copy one neighbour-CTA region into local shared memory (cluster kernels only)
 template <class CF>
-__device__ __forceinline__ void pull_floats(float* dst, const float* src_remote_local_addr, int n,
-                                            unsigned src_rank) {
-    const float2* src = reinterpret_cast<const float2*>(map_rank<CF::CL>(src_remote_local_addr, src_rank));
+__device__ __forceinline__ void pull_floats(float* dst, float* src_local_addr, int n, unsigned src_rank) {
+    const float2* src = reinterpret_cast<const float2*>(map_rank<CF::CL>(src_local_addr, src_rank));
     float2* d = reinterpret_cast<float2*>(dst);
     for (int q = threadIdx.x; q < n / 2; q += CF::NT) d[q] = src[q];
 }
@@ -213,18 +229,20 @@ __device__ __forceinline__ void pull_pd(float* smem, int dst_slot, int src_slot,
 // Leaves S rows and gamma in registers and the Pinv rows in PROW; writes G^-1 in place.
 // ---------------------------------------------------------------------------------------
 template <class CF>
-__device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N, float rho, Rows& R) {
+__device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N, float rho,
+                                           Rows<CF::RPT>& R) {
     constexpr int S = 14, C = 7, KPC = CF::KPC, CL = CF::CL, PR = CF::PR, PK = CF::PK, TK = CF::TK;
+    constexpr int LPK = CF::LPK, RPT = CF::RPT, RPT7 = CF::RPT7;
     constexpr int SS = S * S, CC = C * C, SC = S * C;
     constexpr int GSET = SS + CC, CSET = SS + SC, gSET = S + C;
     constexpr int cD = CF::cD, cL = CF::cL, cR = CF::cR;
     const int tid = threadIdx.x;
-    const int g = tid >> 3, t = tid & 7;
+    const int g = tid / LPK, t = tid % LPK;
     const unsigned rank = cluster_rank<CL>();
     const int k0 = rank * KPC;
     const int k = k0 + g;
-    const bool act = t < 7;
-    const int r0 = act ? t : 0, r1 = r0 + 7;      // idle lane shadows rows 0 / 7 (never writes)
+    const RowMap<LPK, RPT, 14> rm(t);
+    const RowMap<LPK, RPT7, 7> rm7(t);
     const bool valid = k < N;
     const bool inner = valid && k >= 1;
     const bool has_right = valid && (k + 1 < N);
@@ -238,7 +256,7 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     float* vq = myP + 0 * PR + cR;                // q_k
     float* vqm = myP + 1 * PR + cR;               // q_{k-1}
     float* vc = myP + 2 * PR + cR;                // c_k
-    float* vrm = myP + 3 * PR + cR;               // r_{k-1} (7)
+    float* vrm = myP + 3 * PR + cR;               // r_{k-1} (7, padded to 8)
     float* piv = myP + 4 * PR + cR;               // pivot row broadcast (16 B aligned, + 2 pad)
     // B_{k-1} column m: myP[m*PR + cL .. +13] (m < 7); Rt^-1 row m: myP[(7+m)*PR + cL .. +7]
 
@@ -255,65 +273,79 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     for (int q = tid; q < 2 * PK; q += CF::NT) PW[(q < PK) ? q : (KPC + 1) * PK + (q - PK)] = 0.f;
     for (int q = tid; q < 2 * TK; q += CF::NT) TA[(q < TK) ? q : (KPC + 1) * TK + (q - TK)] = 0.f;
 
-    // ---- loads: Qt_k rows, Rt_{k-1} row, vectors -----------------------------------------
-    float2 aQ0[7], aQ1[7];
+    // ---- loads: Qt_k rows, Rt_{k-1} rows, vectors ------------------------------------------
+    float2 aQ[RPT][7];
 #pragma unroll
-    for (int j = 0; j < 14; j++) {
-        float v0 = 0.f, v1 = 0.f;
-        if (valid && act) { v0 = P.G[(size_t)k * GSET + j * S + r0]; v1 = P.G[(size_t)k * GSET + j * S + r1]; }
-        setp(aQ0, j, v0 + ((j == r0) ? rho : 0.f));                    // linsys_setup.cuh:180,329-330
-        setp(aQ1, j, v1 + ((j == r1) ? rho : 0.f));
-    }
-    float aR[8];
+    for (int j = 0; j < RPT; j++) {
 #pragma unroll
-    for (int j = 0; j < 7; j++) {
-        float v = 0.f;
-        if (inner && act) v = P.G[(size_t)(k - 1) * GSET + SS + j * C + r0];
-        aR[j] = v + ((j == r0) ? rho : 0.f);                           // :331
-    }
-    aR[7] = 0.f;
-    __syncthreads();                               // staging done (vectors overwrite zeroed chunks)
-    if (act) {
-        vq[r0] = valid ? __ldg(P.g + (size_t)k * gSET + r0) : 0.f;
-        vq[r1] = valid ? __ldg(P.g + (size_t)k * gSET + r1) : 0.f;
-        vqm[r0] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + r0) : 0.f;
-        vqm[r1] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + r1) : 0.f;
-        vc[r0] = inner ? __ldg(P.c + (size_t)k * S + r0) : 0.f;
-        vc[r1] = inner ? __ldg(P.c + (size_t)k * S + r1) : 0.f;
-        vrm[r0] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + S + r0) : 0.f;
-    }
-    if (t == 7) vrm[7] = 0.f;
-    // knot 0: Pinv[0][1] = -Qt_0, stored BEFORE inversion (linsys_setup.cuh:202-210); its A
-    // tile is unused, park the rows there
-    if (k == 0 && act) { st14_v2(myT + r0 * S, aQ0); st14_v2(myT + r1 * S, aQ1); }
-
-    // ---- phase 1a: inverses ---------------------------------------------------------------
-    gj14(aQ0, aQ1, t, act, piv);                                       // Qt_k^-1
-    gj7(aR, t, act, piv);                                              // Rt_{k-1}^-1
-    if (valid && act) {
-#pragma unroll
-        for (int j = 0; j < 14; j++) {                                 // :372,:379
-            P.G[(size_t)k * GSET + j * S + r0] = getp(aQ0, j);
-            P.G[(size_t)k * GSET + j * S + r1] = getp(aQ1, j);
+        for (int c = 0; c < 14; c++) {
+            float v = 0.f;
+            if (valid && rm.ok[j]) v = P.G[(size_t)k * GSET + c * S + rm.row[j]];
+            setp(aQ[j], c, v + ((c == t + LPK * j) ? rho : 0.f));       // linsys_setup.cuh:180,329-330
         }
     }
-    if (inner && act) {
+    float aR[RPT7][8];
 #pragma unroll
-        for (int j = 0; j < 7; j++) P.G[(size_t)(k - 1) * GSET + SS + j * C + r0] = aR[j];   // :375
+    for (int j = 0; j < RPT7; j++) {
+#pragma unroll
+        for (int c = 0; c < 7; c++) {
+            float v = 0.f;
+            if (inner && rm7.ok[j]) v = P.G[(size_t)(k - 1) * GSET + SS + c * C + rm7.row[j]];
+            aR[j][c] = v + ((c == t + LPK * j) ? rho : 0.f);            // :331
+        }
+        aR[j][7] = 0.f;
     }
-    if (act) {
-        st14_v4(myP + r0 * PR + cD, aQ0);
-        st14_v4(myP + r1 * PR + cD, aQ1);
-        float2* rr = reinterpret_cast<float2*>(myP + (7 + r0) * PR + cL);
-        rr[0] = f2(aR[0], aR[1]); rr[1] = f2(aR[2], aR[3]); rr[2] = f2(aR[4], aR[5]); rr[3] = f2(aR[6], 0.f);
+    __syncthreads();                               // staging done (vectors overwrite zeroed chunks)
+#pragma unroll
+    for (int j = 0; j < RPT; j++) {
+        if (rm.ok[j]) {
+            const int r = rm.row[j];
+            vq[r] = valid ? __ldg(P.g + (size_t)k * gSET + r) : 0.f;
+            vqm[r] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + r) : 0.f;
+            vc[r] = inner ? __ldg(P.c + (size_t)k * S + r) : 0.f;
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < RPT7; j++)
+        if (rm7.ok[j]) vrm[rm7.row[j]] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + S + rm7.row[j]) : 0.f;
+    if (t == 0) vrm[7] = 0.f;
+    // knot 0: Pinv[0][1] = -Qt_0, stored BEFORE inversion (linsys_setup.cuh:202-210); its A
+    // tile is unused, park the rows there
+    if (k == 0) {
+#pragma unroll
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) st14_v2(myT + rm.row[j] * S, aQ[j]);
+    }
+
+    // ---- phase 1a: inverses ---------------------------------------------------------------
+    gj14<LPK, RPT>(aQ, t, piv);                                        // Qt_k^-1
+    gj7<LPK, RPT7>(aR, t, piv);                                        // Rt_{k-1}^-1
+#pragma unroll
+    for (int j = 0; j < RPT; j++) {
+        if (valid && rm.ok[j]) {
+#pragma unroll
+            for (int c = 0; c < 14; c++) P.G[(size_t)k * GSET + c * S + rm.row[j]] = getp(aQ[j], c);   // :372,:379
+        }
+        if (rm.ok[j]) st14_v4(myP + rm.row[j] * PR + cD, aQ[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < RPT7; j++) {
+        if (inner && rm7.ok[j]) {
+#pragma unroll
+            for (int c = 0; c < 7; c++) P.G[(size_t)(k - 1) * GSET + SS + c * C + rm7.row[j]] = aR[j][c];   // :375
+        }
+        if (rm7.ok[j]) {
+            float2* rr = reinterpret_cast<float2*>(myP + (7 + rm7.row[j]) * PR + cL);
+            rr[0] = f2(aR[j][0], aR[j][1]); rr[1] = f2(aR[j][2], aR[j][3]);
+            rr[2] = f2(aR[j][4], aR[j][5]); rr[3] = f2(aR[j][6], 0.f);
+        }
     }
     __syncwarp();
-    float ti0, ti1;                                                    // Qt_k^-1 q_k  (:411-415, :260)
+    float ti[RPT];                                                     // Qt_k^-1 q_k  (:411-415, :260)
     {
         float2 x[7];
         ld14_v4(x, vq);
-        const float2 s0 = dot14_acc(aQ0, x, splat(0.f)), s1 = dot14_acc(aQ1, x, splat(0.f));
-        ti0 = s0.x + s0.y; ti1 = s1.x + s1.y;
+#pragma unroll
+        for (int j = 0; j < RPT; j++) ti[j] = hsum(dot14_acc(aQ[j], x, splat(0.f)));
     }
 
     cluster_sync_all<CL>();
@@ -323,80 +355,98 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     }
 
     // ---- phase 1b: phi, theta, gamma, theta^-1 ----------------------------------------------
-    float2 th0[7], th1[7];
+    float2 th[RPT][7];
     {
-        float2 phi0[7], phi1[7];
+        float2 phi[RPT][7];
 #pragma unroll
-        for (int q = 0; q < 7; q++) { phi0[q] = splat(0.f); phi1[q] = splat(0.f); th0[q] = aQ0[q]; th1[q] = aQ1[q]; }   // + Qt_k^-1 (:466)
+        for (int j = 0; j < RPT; j++)
+#pragma unroll
+            for (int q = 0; q < 7; q++) { phi[j][q] = splat(0.f); th[j][q] = aQ[j][q]; }   // + Qt_k^-1 (:466)
         const float* Qm = PW + (sl - 1) * PK + cD;                     // Qt_{k-1}^-1 rows
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // phi = A Qt_{k-1}^-1   (:398)
             float2 b[7];
             ld14_v4(b, Qm + m * PR);
-            axpy2(phi0, phi1, myT[m * S + r0], myT[m * S + r1], b);
-        }
-        float br0[7], br1[7];
+            float a[RPT];
 #pragma unroll
-        for (int j = 0; j < 7; j++) { br0[j] = 0.f; br1[j] = 0.f; }
+            for (int j = 0; j < RPT; j++) a[j] = myT[m * S + rm.row[j]];
+            axpy_rows<RPT>(phi, a, b);
+        }
+        float br[RPT][7];
+#pragma unroll
+        for (int j = 0; j < RPT; j++)
+#pragma unroll
+            for (int c = 0; c < 7; c++) br[j][c] = 0.f;
 #pragma unroll
         for (int m = 0; m < 7; m++) {                                  // BR = B Rt_{k-1}^-1    (:406)
-            const float b0 = myP[m * PR + cL + r0], b1 = myP[m * PR + cL + r1];
             const float2* rr = reinterpret_cast<const float2*>(myP + (7 + m) * PR + cL);
             const float2 u0 = rr[0], u1 = rr[1], u2 = rr[2], u3 = rr[3];
-            const float rm[7] = {u0.x, u0.y, u1.x, u1.y, u2.x, u2.y, u3.x};
+            const float rmv[7] = {u0.x, u0.y, u1.x, u1.y, u2.x, u2.y, u3.x};
 #pragma unroll
-            for (int j = 0; j < 7; j++) { br0[j] = fmaf(b0, rm[j], br0[j]); br1[j] = fmaf(b1, rm[j], br1[j]); }
+            for (int j = 0; j < RPT; j++) {
+                const float b = myP[m * PR + cL + rm.row[j]];
+#pragma unroll
+                for (int c = 0; c < 7; c++) br[j][c] = fmaf(b, rmv[c], br[j][c]);
+            }
         }
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // + phi A^T             (:447)
             float2 b[7];
             ld14_v2(b, myT + m * S);                                   // column m of A
-            axpy2(th0, th1, getp(phi0, m), getp(phi1, m), b);
+            float a[RPT];
+#pragma unroll
+            for (int j = 0; j < RPT; j++) a[j] = getp(phi[j], m);
+            axpy_rows<RPT>(th, a, b);
         }
 #pragma unroll
         for (int m = 0; m < 7; m++) {                                  // + BR B^T              (:473,:485)
             float2 b[7];
             ld14_v2(b, myP + m * PR + cL);                             // column m of B
-            axpy2(th0, th1, br0[m], br1[m], b);
+            float a[RPT];
+#pragma unroll
+            for (int j = 0; j < RPT; j++) a[j] = br[j][m];
+            axpy_rows<RPT>(th, a, b);
         }
         // gamma  (:416-443)
-        float gm0, gm1;
         {
             float2 x[7];
             ld14_v4(x, vqm);
-            const float2 s0 = dot14_acc(phi0, x, splat(0.f)), s1 = dot14_acc(phi1, x, splat(0.f));
             const float4 ra = reinterpret_cast<const float4*>(vrm)[0], rb = reinterpret_cast<const float4*>(vrm)[1];
             const float rv[7] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z};
-            float d0 = 0.f, d1 = 0.f;
 #pragma unroll
-            for (int j = 0; j < 7; j++) { d0 = fmaf(br0[j], rv[j], d0); d1 = fmaf(br1[j], rv[j], d1); }
-            gm0 = (ti0 - vc[r0]) + (d0 + (s0.x + s0.y));
-            gm1 = (ti1 - vc[r1]) + (d1 + (s1.x + s1.y));
+            for (int j = 0; j < RPT; j++) {
+                const float s = hsum(dot14_acc(phi[j], x, splat(0.f)));
+                float d = 0.f;
+#pragma unroll
+                for (int c = 0; c < 7; c++) d = fmaf(br[j][c], rv[c], d);
+                const float gm = (ti[j] - vc[rm.row[j]]) + (d + s);
+                R.gamma[j] = inner ? -gm : -ti[j];                     // :531 / :274
+            }
         }
-        if (inner) {
 #pragma unroll
-            for (int q = 0; q < 7; q++) { R.Sd[0][q] = f2(-th0[q].x, -th0[q].y); R.Sd[1][q] = f2(-th1[q].x, -th1[q].y); }   // :501
-            R.gamma[0] = -gm0; R.gamma[1] = -gm1;                                                    // :531
-        } else {
+        for (int j = 0; j < RPT; j++)
 #pragma unroll
-            for (int q = 0; q < 7; q++) { R.Sd[0][q] = f2(-aQ0[q].x, -aQ0[q].y); R.Sd[1][q] = f2(-aQ1[q].x, -aQ1[q].y); }   // :249
-            R.gamma[0] = -ti0; R.gamma[1] = -ti1;                                                    // :274
-        }
+            for (int q = 0; q < 7; q++) R.Sd[j][q] = inner ? neg2(th[j][q]) : neg2(aQ[j][q]);   // :501 / :249
         // phi rows replace A in this knot's tile (only this knot's lanes read A): S[k][0] = -phi (:491)
         __syncwarp();
-        if (k != 0 && act) { st14_v2(myT + r0 * S, phi0); st14_v2(myT + r1 * S, phi1); }
+        if (k != 0) {
+#pragma unroll
+            for (int j = 0; j < RPT; j++) if (rm.ok[j]) st14_v2(myT + rm.row[j] * S, phi[j]);
+        }
     }
-    gj14(th0, th1, t, act, piv);                                       // theta_k^-1            (:511-513)
+    gj14<LPK, RPT>(th, t, piv);                                        // theta_k^-1            (:511-513)
 
     cluster_sync_all<CL>();                        // every knot (and every CTA's halo pull) is done with Qt^-1
     // Pd rows: -theta_k^-1 (:518-524), knot 0: -Qt_0 (:202-210)
-    if (k == 0) { ld14_v2(th0, myT + r0 * S); ld14_v2(th1, myT + r1 * S); }
-    if (act) {
-        float2 n0[7], n1[7];
 #pragma unroll
-        for (int q = 0; q < 7; q++) { n0[q] = f2(-th0[q].x, -th0[q].y); n1[q] = f2(-th1[q].x, -th1[q].y); }
-        st14_v4(myP + r0 * PR + cD, n0);
-        st14_v4(myP + r1 * PR + cD, n1);
+    for (int j = 0; j < RPT; j++) {
+        if (k == 0) ld14_v2(th[j], myT + rm.row[j] * S);
+        if (rm.ok[j]) {
+            float2 n[7];
+#pragma unroll
+            for (int q = 0; q < 7; q++) n[q] = neg2(th[j][q]);
+            st14_v4(myP + rm.row[j] * PR + cD, n);
+        }
     }
     cluster_sync_all<CL>();
     if (CL > 1) {
@@ -407,71 +457,82 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
 
     // ---- phase 2: Pinv left block = theta_k^-1 phi_k theta_{k-1}^-1 (stored sign, :97-115) ----
     {
-        float2 t10[7], t11[7], pl0[7], pl1[7];
+        float2 t1[RPT][7], pl[RPT][7];
 #pragma unroll
-        for (int q = 0; q < 7; q++) { t10[q] = splat(0.f); t11[q] = splat(0.f); pl0[q] = splat(0.f); pl1[q] = splat(0.f); }
+        for (int j = 0; j < RPT; j++)
+#pragma unroll
+            for (int q = 0; q < 7; q++) { t1[j][q] = splat(0.f); pl[j][q] = splat(0.f); }
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // theta_k^-1 phi_k        (:100)
             float2 b[7];
             ld14_v2(b, myT + m * S);
-            axpy2(t10, t11, getp(th0, m), getp(th1, m), b);
+            float a[RPT];
+#pragma unroll
+            for (int j = 0; j < RPT; j++) a[j] = getp(th[j], m);
+            axpy_rows<RPT>(t1, a, b);
         }
         const float* Pm = PW + (sl - 1) * PK + cD;                     // -theta_{k-1}^-1 rows
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // ... theta_{k-1}^-1      (:102)
             float2 b[7];
             ld14_v4(b, Pm + m * PR);
-            axpy2(pl0, pl1, -getp(t10, m), -getp(t11, m), b);
-        }
-        if (!inner) {
+            float a[RPT];
 #pragma unroll
-            for (int q = 0; q < 7; q++) { pl0[q] = splat(0.f); pl1[q] = splat(0.f); }
+            for (int j = 0; j < RPT; j++) a[j] = -getp(t1[j], m);
+            axpy_rows<RPT>(pl, a, b);
         }
         // own rows -> Pl columns; transposed -> Pr columns of the left neighbour (:118-136 by symmetry)
-        if (act) {
-            st14_v2(myP + r0 * PR + cL, pl0);
-            st14_v2(myP + r1 * PR + cL, pl1);
-            float* left = PW + (sl - 1) * PK + cR;
-            if (CL > 1 && g == 0 && rank > 0) left = map_rank<CL>(PW + KPC * PK + cR, rank - 1);
+        float* left = PW + (sl - 1) * PK + cR;
+        if (CL > 1 && g == 0 && rank > 0) left = map_rank<CL>(PW + KPC * PK + cR, rank - 1);
 #pragma unroll
-            for (int j = 0; j < 14; j++) { left[j * PR + r0] = getp(pl0, j); left[j * PR + r1] = getp(pl1, j); }
+        for (int j = 0; j < RPT; j++) {
+            if (!inner) {
+#pragma unroll
+                for (int q = 0; q < 7; q++) pl[j][q] = splat(0.f);
+            }
+            if (rm.ok[j]) {
+                st14_v2(myP + rm.row[j] * PR + cL, pl[j]);
+#pragma unroll
+                for (int c = 0; c < 14; c++) left[c * PR + rm.row[j]] = getp(pl[j], c);
+            }
         }
     }
     // last valid knot (and padding knots): no right neighbour writes their Pr columns
-    if (!has_right && act) {
+    if (!has_right) {
 #pragma unroll
-        for (int j = 0; j < 14; j++) { myP[j * PR + cR + r0] = 0.f; myP[j * PR + cR + r1] = 0.f; }
+        for (int j = 0; j < RPT; j++)
+            if (rm.ok[j]) {
+#pragma unroll
+                for (int c = 0; c < 14; c++) myP[c * PR + cR + rm.row[j]] = 0.f;
+            }
     }
     // ---- S left rows (own phi rows) and right rows (-phi_{k+1}^T, :537-557) ------------------
     {
-        float2 a[7], b[7];
-        ld14_v2(a, myT + r0 * S); ld14_v2(b, myT + r1 * S);
-#pragma unroll
-        for (int q = 0; q < 7; q++) {
-            R.Sl[0][q] = inner ? f2(-a[q].x, -a[q].y) : splat(0.f);
-            R.Sl[1][q] = inner ? f2(-b[q].x, -b[q].y) : splat(0.f);
-        }
         const float* phin = TA + (sl + 1) * TK;
 #pragma unroll
-        for (int j = 0; j < 14; j++) {
-            setp(R.Sr[0], j, has_right ? -phin[j * S + r0] : 0.f);
-            setp(R.Sr[1], j, has_right ? -phin[j * S + r1] : 0.f);
-        }
-    }
-    if (!valid || !act) {
+        for (int j = 0; j < RPT; j++) {
+            float2 a[7];
+            ld14_v2(a, myT + rm.row[j] * S);
+            const bool on = valid && rm.ok[j];
 #pragma unroll
-        for (int q = 0; q < 7; q++) {
-            R.Sl[0][q] = R.Sl[1][q] = R.Sd[0][q] = R.Sd[1][q] = R.Sr[0][q] = R.Sr[1][q] = splat(0.f);
+            for (int q = 0; q < 7; q++) R.Sl[j][q] = (inner && rm.ok[j]) ? neg2(a[q]) : splat(0.f);
+#pragma unroll
+            for (int c = 0; c < 14; c++) setp(R.Sr[j], c, (has_right && rm.ok[j]) ? -phin[c * S + rm.row[j]] : 0.f);
+            if (!on) {
+#pragma unroll
+                for (int q = 0; q < 7; q++) R.Sd[j][q] = splat(0.f);
+                R.gamma[j] = 0.f;
+            }
         }
-        R.gamma[0] = R.gamma[1] = 0.f;
     }
     cluster_sync_all<CL>();                        // PROW complete (incl. rows scattered by neighbours)
-    if (!valid && act) {                           // padding knots: zero Pinv rows (their Pd holds 1/rho junk)
+    if (!valid) {                                  // padding knots: zero Pinv rows (their Pd holds 1/rho junk)
 #pragma unroll
-        for (int q = 0; q < 11; q++) {
-            reinterpret_cast<float4*>(myP + r0 * PR)[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-            reinterpret_cast<float4*>(myP + r1 * PR)[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+        for (int j = 0; j < RPT; j++)
+            if (rm.ok[j]) {
+#pragma unroll
+                for (int q = 0; q < 11; q++) reinterpret_cast<float4*>(myP + rm.row[j] * PR)[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+            }
     }
 }
 
@@ -514,16 +575,17 @@ __device__ __forceinline__ float cluster_sum(float* red, int buf, float val, uns
 // locally and need no further exchange.
 // ---------------------------------------------------------------------------------------
 template <class CF>
-__device__ __forceinline__ void pcg_rows(float* smem, const Rows& R, float* lam_g, int N,
+__device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, float* lam_g, int N,
                                          unsigned max_iter, float exit_tol, unsigned* d_iters,
                                          uint8_t* d_exit) {
     constexpr int S = 14, KPC = CF::KPC, CL = CF::CL, PR = CF::PR, PK = CF::PK, VK = CF::VK;
+    constexpr int LPK = CF::LPK, RPT = CF::RPT;
     const int tid = threadIdx.x;
-    const int g = tid >> 3, t = tid & 7;
+    const int g = tid / LPK, t = tid % LPK;
     const unsigned rank = cluster_rank<CL>();
     const int k0 = rank * KPC, k = k0 + g;
-    const bool act = t < 7, valid = k < N;
-    const int r0 = act ? t : 0, r1 = r0 + 7;
+    const bool valid = k < N;
+    const RowMap<LPK, RPT, 14> rm(t);
     const bool first_g = (g == 0), last_g = (g == KPC - 1);
     const bool has_l = rank > 0, has_r = rank + 1 < (unsigned)CL;
     const int sl = g + 1;
@@ -532,132 +594,145 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows& R, float* lam_
     float* rv = smem + CF::oRv;
     float* hal = smem + CF::oHal;   // [phase][side][16]; side 0: pushed by my LEFT neighbour CTA
     float* red = smem + CF::oRed;
-    const float* myP0 = smem + CF::oP + sl * PK + r0 * PR;
-    const float* myP1 = smem + CF::oP + sl * PK + r1 * PR;
+    const float* myP = smem + CF::oP + sl * PK;
 
-    // y(rows r0, r1) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
-    auto s_mv = [&](const float* vec, float& y0, float& y1) {
+    // y(rows) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
+    auto s_mv = [&](const float* vec, float (&y)[RPT]) {
         float2 xl[7], xd[7], xr[7];
         ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
-        float2 a0 = dot14_acc(R.Sl[0], xl, splat(0.f)), b0 = dot14_acc(R.Sd[0], xd, splat(0.f)), c0 = dot14_acc(R.Sr[0], xr, splat(0.f));
-        float2 a1 = dot14_acc(R.Sl[1], xl, splat(0.f)), b1 = dot14_acc(R.Sd[1], xd, splat(0.f)), c1 = dot14_acc(R.Sr[1], xr, splat(0.f));
-        y0 = ((a0.x + a0.y) + (b0.x + b0.y)) + (c0.x + c0.y);
-        y1 = ((a1.x + a1.y) + (b1.x + b1.y)) + (c1.x + c1.y);
+#pragma unroll
+        for (int j = 0; j < RPT; j++) {
+            const float2 a = dot14_acc(R.Sl[j], xl, splat(0.f)), b = dot14_acc(R.Sd[j], xd, splat(0.f)),
+                         c = dot14_acc(R.Sr[j], xr, splat(0.f));
+            y[j] = (hsum(a) + hsum(b)) + hsum(c);
+        }
     };
     // same with the Pinv rows from shared memory (row = [Pd | Pl | Pr | pad])
-    auto p_mv = [&](const float* vec, float& y0, float& y1) {
+    auto p_mv = [&](const float* vec, float (&y)[RPT]) {
         float2 xl[7], xd[7], xr[7];
         ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
-        const float4* q0 = reinterpret_cast<const float4*>(myP0);
-        const float4* q1 = reinterpret_cast<const float4*>(myP1);
-        float2 acc0[3] = {splat(0.f), splat(0.f), splat(0.f)}, acc1[3] = {splat(0.f), splat(0.f), splat(0.f)};
 #pragma unroll
-        for (int q = 0; q < 11; q++) {
-            const float4 u = q0[q], v = q1[q];
-            // floats 4q .. 4q+3 of the row: pair indices 2q and 2q+1 of the 21 pairs (Pd 0-6, Pl 7-13, Pr 14-20)
+        for (int j = 0; j < RPT; j++) {
+            const float4* q4 = reinterpret_cast<const float4*>(myP + rm.row[j] * PR);
+            float2 acc[3] = {splat(0.f), splat(0.f), splat(0.f)};
 #pragma unroll
-            for (int h = 0; h < 2; h++) {
-                const int pi = 2 * q + h;
-                if (pi < 21) {
-                    const int part = pi / 7, w = pi % 7;
-                    const float2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
-                    acc0[part] = fma2(h ? f2(u.z, u.w) : f2(u.x, u.y), x, acc0[part]);
-                    acc1[part] = fma2(h ? f2(v.z, v.w) : f2(v.x, v.y), x, acc1[part]);
+            for (int q = 0; q < 11; q++) {
+                const float4 u = q4[q];
+                // floats 4q .. 4q+3 of the row: pairs 2q, 2q+1 of 21 (Pd 0-6, Pl 7-13, Pr 14-20)
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    const int pi = 2 * q + h;
+                    if (pi < 21) {
+                        const int part = pi / 7, w = pi % 7;
+                        const float2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
+                        acc[part] = fma2(h ? f2(u.z, u.w) : f2(u.x, u.y), x, acc[part]);
+                    }
                 }
             }
+            y[j] = rm.ok[j] ? (hsum(acc[1]) + hsum(acc[0])) + hsum(acc[2]) : 0.f;
         }
-        y0 = ((acc0[1].x + acc0[1].y) + (acc0[0].x + acc0[0].y)) + (acc0[2].x + acc0[2].y);
-        y1 = ((acc1[1].x + acc1[1].y) + (acc1[0].x + acc1[0].y)) + (acc1[2].x + acc1[2].y);
+    };
+    auto put = [&](float* dst, const float (&v)[RPT]) {        // my rows of a 16-float vector slot
+#pragma unroll
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) dst[rm.row[j]] = v[j];
+    };
+    auto dotp = [&](const float (&a)[RPT], const float (&b)[RPT]) {
+        float d = 0.f;
+#pragma unroll
+        for (int j = 0; j < RPT; j++) d = fmaf(a[j], b[j], d);   // invalid slots hold zeros
+        return d;
     };
 
-    float* my_p0 = pv + sl * VK + r0; float* my_p1 = pv + sl * VK + r1;
-    float* my_r0 = rv + sl * VK + r0; float* my_r1 = rv + sl * VK + r1;
     float* hl_p = pv;                        // left halo slot
     float* hr_p = pv + (KPC + 1) * VK;       // right halo slot
     float* hl_r = rv;
     float* hr_r = rv + (KPC + 1) * VK;
+    const float zero[RPT] = {};
 
     // ---- r = gamma - S lambda0 --------------------------------------------------------------
-    float lam0 = 0.f, lam1 = 0.f;
-    if (valid && act) { lam0 = lam_g[(size_t)k * S + r0]; lam1 = lam_g[(size_t)k * S + r1]; }
-    if (act) { *my_p0 = lam0; *my_p1 = lam1; }
-    if (t == 7) { pv[sl * VK + 14] = 0.f; pv[sl * VK + 15] = 0.f; rv[sl * VK + 14] = 0.f; rv[sl * VK + 15] = 0.f; }
+    float lam[RPT], rr[RPT], pp[RPT], rt[RPT], y[RPT];
+#pragma unroll
+    for (int j = 0; j < RPT; j++) lam[j] = (valid && rm.ok[j]) ? lam_g[(size_t)k * S + rm.row[j]] : 0.f;
+    put(pv + sl * VK, lam);
     if (first_g) {
-        const bool ok = (k0 >= 1 && k0 - 1 < N && act);
-        if (act) { hl_p[r0] = ok ? lam_g[(size_t)(k0 - 1) * S + r0] : 0.f; hl_p[r1] = ok ? lam_g[(size_t)(k0 - 1) * S + r1] : 0.f; }
-        else { hl_p[14] = hl_p[15] = 0.f; hl_r[14] = hl_r[15] = 0.f; }
+        const bool ok = (k0 >= 1 && k0 - 1 < N);
+#pragma unroll
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) hl_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 - 1) * S + rm.row[j]] : 0.f;
     }
     if (last_g) {
-        const bool ok = (k0 + KPC < N && act);
-        if (act) { hr_p[r0] = ok ? lam_g[(size_t)(k0 + KPC) * S + r0] : 0.f; hr_p[r1] = ok ? lam_g[(size_t)(k0 + KPC) * S + r1] : 0.f; }
-        else { hr_p[14] = hr_p[15] = 0.f; hr_r[14] = hr_r[15] = 0.f; }
+        const bool ok = (k0 + KPC < N);
+#pragma unroll
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) hr_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 + KPC) * S + rm.row[j]] : 0.f;
     }
     __syncthreads();
-    float y0, y1;
-    s_mv(pv, y0, y1);
-    float rr0 = R.gamma[0] - y0, rr1 = R.gamma[1] - y1;
-    if (act) {
-        *my_r0 = rr0; *my_r1 = rr1;
-        if (first_g) { if (has_l) { float* d = map_rank<CL>(hr_r, rank - 1); d[r0] = rr0; d[r1] = rr1; } else { hl_r[r0] = 0.f; hl_r[r1] = 0.f; } }
-        if (last_g)  { if (has_r) { float* d = map_rank<CL>(hl_r, rank + 1); d[r0] = rr0; d[r1] = rr1; } else { hr_r[r0] = 0.f; hr_r[r1] = 0.f; } }
-    }
+    s_mv(pv, y);
+#pragma unroll
+    for (int j = 0; j < RPT; j++) rr[j] = rm.ok[j] ? R.gamma[j] - y[j] : 0.f;
+    put(rv + sl * VK, rr);
+    if (first_g) { if (has_l) put(map_rank<CL>(hr_r, rank - 1), rr); else put(hl_r, zero); }
+    if (last_g)  { if (has_r) put(map_rank<CL>(hl_r, rank + 1), rr); else put(hr_r, zero); }
     cluster_sync_all<CL>();
 
     // ---- p = rt = Pinv r ; eta = r.rt ----------------------------------------------------------
-    float rt0, rt1;
-    p_mv(rv, rt0, rt1);
-    float p0 = rt0, p1 = rt1;
-    if (act) {
-        *my_p0 = p0; *my_p1 = p1;       // pv was last read before the barrier above
-        if (first_g) { if (has_l) { float* d = map_rank<CL>(hr_p, rank - 1); d[r0] = p0; d[r1] = p1; } else { hl_p[r0] = 0.f; hl_p[r1] = 0.f; } }
-        if (last_g)  { if (has_r) { float* d = map_rank<CL>(hl_p, rank + 1); d[r0] = p0; d[r1] = p1; } else { hr_p[r0] = 0.f; hr_p[r1] = 0.f; } }
-    }
-    float eta = cluster_sum<CF>(red, 1, act ? fmaf(rr0, rt0, rr1 * rt1) : 0.f, rank);
+    p_mv(rv, rt);
+#pragma unroll
+    for (int j = 0; j < RPT; j++) pp[j] = rt[j];
+    put(pv + sl * VK, pp);                   // pv was last read before the barrier above
+    if (first_g) { if (has_l) put(map_rank<CL>(hr_p, rank - 1), pp); else put(hl_p, zero); }
+    if (last_g)  { if (has_r) put(map_rank<CL>(hl_p, rank + 1), pp); else put(hr_p, zero); }
+    float eta = cluster_sum<CF>(red, 1, dotp(rr, rt), rank);
 
     unsigned iter = 0;
     bool max_iter_exit = true;
     for (; iter < max_iter; iter++) {
         // ---- ups = S p ; v = p.ups -----------------------------------------------------------
-        float u0, u1;
-        s_mv(pv, u0, u1);
-        if (CL > 1 && act) {
-            if (first_g && has_l) { float* d = map_rank<CL>(hal + (0 * 2 + 1) * VK, rank - 1); d[r0] = u0; d[r1] = u1; }
-            if (last_g && has_r)  { float* d = map_rank<CL>(hal + (0 * 2 + 0) * VK, rank + 1); d[r0] = u0; d[r1] = u1; }
+        s_mv(pv, y);
+        if (CL > 1) {
+            if (first_g && has_l) put(map_rank<CL>(hal + (0 * 2 + 1) * VK, rank - 1), y);
+            if (last_g && has_r)  put(map_rank<CL>(hal + (0 * 2 + 0) * VK, rank + 1), y);
         }
-        const float v = cluster_sum<CF>(red, 0, act ? fmaf(p0, u0, p1 * u1) : 0.f, rank);
+        const float v = cluster_sum<CF>(red, 0, dotp(pp, y), rank);
         if (v == 0.f) { max_iter_exit = false; break; }
         const float alpha = eta / v;
-        lam0 = fmaf(alpha, p0, lam0); lam1 = fmaf(alpha, p1, lam1);
-        rr0 = fmaf(-alpha, u0, rr0); rr1 = fmaf(-alpha, u1, rr1);
-        if (act) {
-            *my_r0 = rr0; *my_r1 = rr1;
-            if (CL > 1) {
-                if (first_g && has_l) { hl_r[r0] = fmaf(-alpha, hal[(0 * 2 + 0) * VK + r0], hl_r[r0]); hl_r[r1] = fmaf(-alpha, hal[(0 * 2 + 0) * VK + r1], hl_r[r1]); }
-                if (last_g && has_r)  { hr_r[r0] = fmaf(-alpha, hal[(0 * 2 + 1) * VK + r0], hr_r[r0]); hr_r[r1] = fmaf(-alpha, hal[(0 * 2 + 1) * VK + r1], hr_r[r1]); }
+#pragma unroll
+        for (int j = 0; j < RPT; j++) { lam[j] = fmaf(alpha, pp[j], lam[j]); rr[j] = fmaf(-alpha, y[j], rr[j]); }
+        put(rv + sl * VK, rr);
+        if (CL > 1) {
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                if (!rm.ok[j]) continue;
+                const int r = rm.row[j];
+                if (first_g && has_l) hl_r[r] = fmaf(-alpha, hal[(0 * 2 + 0) * VK + r], hl_r[r]);
+                if (last_g && has_r)  hr_r[r] = fmaf(-alpha, hal[(0 * 2 + 1) * VK + r], hr_r[r]);
             }
         }
         __syncthreads();
         // ---- rt = Pinv r ; eta_new = r.rt ----------------------------------------------------
-        p_mv(rv, rt0, rt1);
-        if (CL > 1 && act) {
-            if (first_g && has_l) { float* d = map_rank<CL>(hal + (1 * 2 + 1) * VK, rank - 1); d[r0] = rt0; d[r1] = rt1; }
-            if (last_g && has_r)  { float* d = map_rank<CL>(hal + (1 * 2 + 0) * VK, rank + 1); d[r0] = rt0; d[r1] = rt1; }
+        p_mv(rv, rt);
+        if (CL > 1) {
+            if (first_g && has_l) put(map_rank<CL>(hal + (1 * 2 + 1) * VK, rank - 1), rt);
+            if (last_g && has_r)  put(map_rank<CL>(hal + (1 * 2 + 0) * VK, rank + 1), rt);
         }
-        const float eta_new = cluster_sum<CF>(red, 1, act ? fmaf(rr0, rt0, rr1 * rt1) : 0.f, rank);
+        const float eta_new = cluster_sum<CF>(red, 1, dotp(rr, rt), rank);
         if (fabsf(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
         const float beta = eta_new / eta;
         eta = eta_new;
-        p0 = fmaf(beta, p0, rt0); p1 = fmaf(beta, p1, rt1);
-        if (act) {
-            *my_p0 = p0; *my_p1 = p1;
-            if (CL > 1) {
-                if (first_g && has_l) { hl_p[r0] = fmaf(beta, hl_p[r0], hal[(1 * 2 + 0) * VK + r0]); hl_p[r1] = fmaf(beta, hl_p[r1], hal[(1 * 2 + 0) * VK + r1]); }
-                if (last_g && has_r)  { hr_p[r0] = fmaf(beta, hr_p[r0], hal[(1 * 2 + 1) * VK + r0]); hr_p[r1] = fmaf(beta, hr_p[r1], hal[(1 * 2 + 1) * VK + r1]); }
+#pragma unroll
+        for (int j = 0; j < RPT; j++) pp[j] = fmaf(beta, pp[j], rt[j]);
+        put(pv + sl * VK, pp);
+        if (CL > 1) {
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                if (!rm.ok[j]) continue;
+                const int r = rm.row[j];
+                if (first_g && has_l) hl_p[r] = fmaf(beta, hl_p[r], hal[(1 * 2 + 0) * VK + r]);
+                if (last_g && has_r)  hr_p[r] = fmaf(beta, hr_p[r], hal[(1 * 2 + 1) * VK + r]);
             }
         }
         __syncthreads();
     }
-    if (valid && act) { lam_g[(size_t)k * S + r0] = lam0; lam_g[(size_t)k * S + r1] = lam1; }
+#pragma unroll
+    for (int j = 0; j < RPT; j++) if (valid && rm.ok[j]) lam_g[(size_t)k * S + rm.row[j]] = lam[j];
     if (rank == 0 && tid == 0) { *d_iters = iter; *d_exit = max_iter_exit ? 1 : 0; }
     // no CTA may exit while a peer can still address its shared memory
     if (CL > 1) cluster_sync_all<CL>();

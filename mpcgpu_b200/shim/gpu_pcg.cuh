@@ -1,0 +1,125 @@
+// gpu_pcg.cuh -- drop-in for GBD-PCG's include/gpu_pcg.cuh (absent from the reference
+// checkout): the symbols the reference's solver slot uses,
+//     pcg<T, STATE_SIZE, KNOT_POINTS>   kernel; argument list include/pcg/sqp.cuh:150-165
+//     pcgSharedMemSize<T>(s, N)         include/pcg/sqp.cuh:166
+//     checkPcgOccupancy<T>(kernel, block, s, N)   examples/track_iiwa_pcg.cu:24
+// plus pcg_config<T> (types.cuh) and gpuErrchk (gpuassert.cuh).
+//
+// The CALLER fixes the launch geometry: cudaLaunchCooperativeKernel(pcg, grid = knot_points,
+// block = PCG_NUM_THREADS (128), args, pcgSharedMemSize) at include/pcg/sqp.cuh:275.  Inside
+// that geometry this kernel carries a compile-time __cluster_dims__: the first cluster
+// (<= 16 CTAs x 128 threads = 16 knots per CTA, 8 lanes per knot) runs the sm_100a
+// cluster/DSMEM PCG of csrc/kkt_device.cuh on the whole horizon; the surplus CTAs of the
+// caller's grid retire immediately (nothing waits on them: there is no grid-wide barrier).
+// Horizons that do not fit one cluster (N > 256, or N without a usable divisor) and
+// T = double fall back to the cooperative one-CTA-per-knot kernel (csrc/refstyle_pcg.cuh).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
+#include <type_traits>
+
+#include "gpuassert.cuh"
+#include "types.cuh"
+#include "utils.cuh"
+#include "glass.cuh"
+#include "../csrc/kernels.cuh"
+#include "../csrc/refstyle_pcg.cuh"
+
+namespace mpcb200_shim {
+
+constexpr uint32_t KPC = 16;   // knots per 128-thread CTA at 8 lanes per knot
+
+// smallest cluster size that covers N knots, divides the caller's grid (= N) and is <= 16
+__host__ __device__ constexpr uint32_t cluster_for(uint32_t N) {
+    for (uint32_t cl = (N + KPC - 1) / KPC; cl <= 16; cl++)
+        if (cl >= 1 && N % cl == 0) return cl;
+    return 0;   // no cluster tiling: cooperative fallback
+}
+
+template <typename T, uint32_t S, uint32_t N>
+struct Use {
+    static constexpr uint32_t CL = cluster_for(N);
+    static constexpr bool CLUSTER = std::is_same<T, float>::value && S == 14 && CL != 0;
+    static constexpr uint32_t DIM = CLUSTER ? CL : 1;
+};
+
+template <uint32_t N>
+using Tiling = mpcb200::Cfg<KPC, (cluster_for(N) ? cluster_for(N) : 1), 8>;
+
+}  // namespace mpcb200_shim
+
+template <typename T, uint32_t STATE_SIZE_, uint32_t KNOT_POINTS_>
+__global__ void
+__cluster_dims__(mpcb200_shim::Use<T, STATE_SIZE_, KNOT_POINTS_>::DIM, 1, 1)
+__launch_bounds__(128)
+pcg(T* d_S, T* d_Pinv, T* d_gamma, T* d_lambda, T* d_r, T* d_p, T* d_v_temp, T* d_eta_new_temp,
+    uint32_t* d_pcg_iters, bool* d_pcg_exit, uint32_t max_iter, T exit_tol) {
+    extern __shared__ float4 pcg_shim_smem4[];
+    if constexpr (mpcb200_shim::Use<T, STATE_SIZE_, KNOT_POINTS_>::CLUSTER) {
+        using CF = mpcb200_shim::Tiling<KNOT_POINTS_>;
+        if (blockIdx.x >= CF::CL) return;            // surplus clusters of the caller's grid
+        float* smem = reinterpret_cast<float*>(pcg_shim_smem4);
+        mpcb200::Rows<CF::RPT> R;
+        mpcb200::load_rows<CF>(smem, R, d_S, d_Pinv, d_gamma, (int)KNOT_POINTS_);
+        mpcb200::pcg_rows<CF>(smem, R, d_lambda, (int)KNOT_POINTS_, max_iter, exit_tol, d_pcg_iters,
+                              reinterpret_cast<uint8_t*>(d_pcg_exit));
+    } else {
+        mpcb200_refstyle::pcg_body<T>(STATE_SIZE_, KNOT_POINTS_, d_S, d_Pinv, d_gamma, d_lambda, d_r, d_p,
+                                      d_v_temp, d_eta_new_temp, d_pcg_iters, d_pcg_exit, max_iter,
+                                      exit_tol, reinterpret_cast<T*>(pcg_shim_smem4));
+    }
+}
+
+#if defined(STATE_SIZE) && defined(KNOT_POINTS)
+#define MPCB200_SHIM_HAVE_DIMS 1
+#else
+#define MPCB200_SHIM_HAVE_DIMS 0
+#endif
+
+// dynamic shared memory of pcg<T, state_size, knot_points>
+template <typename T>
+size_t pcgSharedMemSize(uint32_t state_size, uint32_t knot_points) {
+    size_t bytes = sizeof(T) * mpcb200_refstyle::smem_elems<T>(state_size);
+    if (std::is_same<T, float>::value && state_size == 14 && mpcb200_shim::cluster_for(knot_points) != 0) {
+        const size_t slots = mpcb200_shim::KPC + 2;
+        const size_t cl = mpcb200_shim::cluster_for(knot_points);
+        // == Cfg<16, cl, 8>::SMEM_BYTES (kept in closed form because knot_points is a run-time value here)
+        bytes = sizeof(float) * (slots * (624 + 196 + 16 + 16) + 4 * 16 + 2 * ((cl * 4 + 3) & ~size_t(3)));
+    }
+#if MPCB200_SHIM_HAVE_DIMS
+    // the reference launches with more than the 48 KB default and with cluster sizes up to 16:
+    // opt in once per process (callers that skip checkPcgOccupancy still work)
+    static bool configured = false;
+    if (!configured && state_size == STATE_SIZE && knot_points == KNOT_POINTS) {
+        void* k = (void*)pcg<T, STATE_SIZE, KNOT_POINTS>;
+        gpuErrchk(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+        if (mpcb200_shim::cluster_for(knot_points) > 8)
+            gpuErrchk(cudaFuncSetAttribute(k, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        configured = true;
+    }
+#endif
+    return bytes;
+}
+
+// host check before the run (examples/track_iiwa_pcg.cu:24): the cooperative launch of
+// `knot_points` CTAs must be co-resident; also opts the kernel in to its shared-memory size.
+template <typename T>
+bool checkPcgOccupancy(void* kernel, unsigned block, uint32_t state_size, uint32_t knot_points) {
+    const size_t smem = pcgSharedMemSize<T>(state_size, knot_points);
+    gpuErrchk(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (mpcb200_shim::cluster_for(knot_points) > 8)
+        gpuErrchk(cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+    int dev = 0, sms = 0, per_sm = 0, coop = 0;
+    gpuErrchk(cudaGetDevice(&dev));
+    gpuErrchk(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    gpuErrchk(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev));
+    gpuErrchk(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, (int)block, smem));
+    if (!coop || (uint32_t)(per_sm * sms) < knot_points) {
+        fprintf(stderr, "pcg: %u CTAs of %u threads (%zu B smem) are not co-resident on this device "
+                        "(%d SMs x %d CTAs): reduce KNOT_POINTS\n", knot_points, block, smem, sms, per_sm);
+        exit(7);
+    }
+    return true;
+}
