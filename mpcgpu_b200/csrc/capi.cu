@@ -63,42 +63,44 @@ cudaError_t launch(const BatchArgs& a, cudaStream_t st) {
     return e;
 }
 
-// (KPC, CL, LPK) tiling: N <= KPC*CL.  Default: 64 knots per CTA, 4 lanes per knot (a 64-knot
-// instance lives in one SM with 256 threads, no cluster barrier at all).  The environment
-// variable MPCGPU_B200_TILING=<kpc>x<lpk> (e.g. 32x8) selects other tilings for experiments.
+// (KPC, CL, LPK) tiling: N <= KPC*CL.
+//  * throughput tiling (many instances): 64 knots per CTA -- a 64-knot instance lives in ONE SM,
+//    no cluster barrier at all; lanes per knot from MPCGPU_B200_LPK (4 or 8).
+//  * latency tiling (the whole batch fits one wave of 16-knot CTAs): 16 knots per 128-thread
+//    CTA, cluster of N/16 CTAs (<= 16) -- the per-iteration shared-memory time scales with the
+//    knots per CTA, so a single solve spreads over as many SMs as a cluster allows.
 template <int KIND>
 cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
-    static const int pref = [] {
-        const char* e = getenv("MPCGPU_B200_TILING");
-        int kpc = 64, lpk = 4;
-        if (e && sscanf(e, "%dx%d", &kpc, &lpk) != 2) { kpc = 64; lpk = 4; }
-        return kpc * 100 + lpk;
+    static const int lpk = [] {
+        const char* e = getenv("MPCGPU_B200_LPK");
+        return (e && atoi(e) == 4) ? 4 : 8;
+    }();
+    static const int lat = [] {
+        const char* e = getenv("MPCGPU_B200_LATENCY_TILING");
+        return e ? atoi(e) : -1;      // -1: automatic, 0: never, 1: always
     }();
     const int N = a.N;
-    if (pref == 6408) {
-        if (N <= 64) return launch<Cfg<64, 1, 8>, KIND>(a, st);
-        if (N <= 128) return launch<Cfg<64, 2, 8>, KIND>(a, st);
-        if (N <= 256) return launch<Cfg<64, 4, 8>, KIND>(a, st);
-        if (N <= 512) return launch<Cfg<64, 8, 8>, KIND>(a, st);
-    }
-    if (pref == 3208) {
-        if (N <= 32) return launch<Cfg<32, 1, 8>, KIND>(a, st);
-        if (N <= 64) return launch<Cfg<32, 2, 8>, KIND>(a, st);
-        if (N <= 128) return launch<Cfg<32, 4, 8>, KIND>(a, st);
-        if (N <= 256) return launch<Cfg<32, 8, 8>, KIND>(a, st);
-    }
-    if (pref == 3204) {
-        if (N <= 32) return launch<Cfg<32, 1, 4>, KIND>(a, st);
-        if (N <= 64) return launch<Cfg<32, 2, 4>, KIND>(a, st);
-        if (N <= 128) return launch<Cfg<32, 4, 4>, KIND>(a, st);
-        if (N <= 256) return launch<Cfg<32, 8, 4>, KIND>(a, st);
+    const int cl_lat = (N + 15) / 16;
+    const bool latency = lat == 1 || (lat != 0 && (long long)a.batch * cl_lat <= 148);
+    if (latency) {
+        if (N <= 16) return launch<Cfg<16, 1, 8>, KIND>(a, st);
+        if (N <= 32) return launch<Cfg<16, 2, 8>, KIND>(a, st);
+        if (N <= 64) return launch<Cfg<16, 4, 8>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<16, 8, 8>, KIND>(a, st);
+        if (N <= 256) return launch<Cfg<16, 16, 8>, KIND>(a, st);
+        if (N <= 512) return launch<Cfg<32, 16, 8>, KIND>(a, st);
     }
     if (N <= 16) return launch<Cfg<16, 1, 8>, KIND>(a, st);
-    if (N <= 32) return launch<Cfg<32, 1, 4>, KIND>(a, st);
-    if (N <= 64) return launch<Cfg<64, 1, 4>, KIND>(a, st);
-    if (N <= 128) return launch<Cfg<64, 2, 4>, KIND>(a, st);
-    if (N <= 256) return launch<Cfg<64, 4, 4>, KIND>(a, st);
-    if (N <= 512) return launch<Cfg<64, 8, 4>, KIND>(a, st);
+    if (N <= 32) return launch<Cfg<32, 1, 8>, KIND>(a, st);
+    if (lpk == 4) {
+        if (N <= 64) return launch<Cfg<64, 1, 4>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<64, 2, 4>, KIND>(a, st);
+    } else {
+        if (N <= 64) return launch<Cfg<64, 1, 8>, KIND>(a, st);
+        if (N <= 128) return launch<Cfg<64, 2, 8>, KIND>(a, st);
+    }
+    if (N <= 256) return launch<Cfg<64, 4, 8>, KIND>(a, st);
+    if (N <= 512) return launch<Cfg<64, 8, 8>, KIND>(a, st);
     return cudaErrorInvalidValue;
 }
 

@@ -84,14 +84,24 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
         }
         R.gamma[j] = on ? __ldg(gam + (size_t)k * S + r) : 0.f;
     }
-    for (int e = threadIdx.x; e < CF::KPC * 3 * SS; e += CF::NT) {
-        const int gg = e / (3 * SS), w = e - gg * 3 * SS;
-        const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
-        const int kk = k0 + gg;
-        const bool corner = (kk == 0 && blk == 0) || (kk == N - 1 && blk == 2);
-        float v = 0.f;
-        if (kk < N && !corner) v = __ldg(Pg + (size_t)kk * 3 * SS + w);
-        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j] = v;
+    {
+        constexpr int TOT2 = CF::KPC * 3 * SS / 2, ITERS = (TOT2 + CF::NT - 1) / CF::NT;
+        const float2* src = reinterpret_cast<const float2*>(Pg + (size_t)k0 * 3 * SS);
+#pragma unroll 8
+        for (int it = 0; it < ITERS; it++) {
+            const int e2 = threadIdx.x + it * CF::NT;
+            if (e2 < TOT2) {
+                const int e = 2 * e2;
+                const int gg = e / (3 * SS), w = e - gg * 3 * SS;
+                const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
+                const int kk = k0 + gg;
+                const bool corner = (kk == 0 && blk == 0) || (kk == N - 1 && blk == 2);
+                float2 v = make_float2(0.f, 0.f);
+                if (kk < N && !corner) v = __ldg(src + e2);
+                float* d = smem + CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j;
+                d[0] = v.x; d[CF::PR] = v.y;
+            }
+        }
     }
     for (int e = threadIdx.x; e < CF::KPC * S; e += CF::NT) {      // row padding (never used in sums)
         const int gg = e / S, i = e - gg * S;

@@ -131,14 +131,15 @@ __device__ __forceinline__ void axpy_rows(float2 (&c)[RPT][7], const float (&a)[
 }
 
 // Row bookkeeping of a lane: slot j holds row t + LPK*j (rows >= D do not exist; such slots
-// shadow row 0 for addressing, never store, and carry zeros into every sum).
+// shadow lane 0's row of that slot for addressing (same address: a broadcast, no bank
+// conflict), never store, and carry zeros into every sum).
 template <int LPK, int RPT, int D>
 struct RowMap {
     int row[RPT];
     bool ok[RPT];
     __device__ __forceinline__ RowMap(int t) {
 #pragma unroll
-        for (int j = 0; j < RPT; j++) { const int r = t + LPK * j; ok[j] = r < D; row[j] = ok[j] ? r : 0; }
+        for (int j = 0; j < RPT; j++) { const int r = t + LPK * j; ok[j] = r < D; row[j] = ok[j] ? r : LPK * j; }
     }
 };
 
@@ -261,13 +262,27 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     // B_{k-1} column m: myP[m*PR + cL .. +13] (m < 7); Rt^-1 row m: myP[(7+m)*PR + cL .. +7]
 
     // ---- stage [Abar_{k-1} | Bbar_{k-1}] (one contiguous run per knot), coalesced ----------
-    for (int idx = tid; idx < KPC * CSET; idx += CF::NT) {
-        const int gg = idx / CSET, e = idx - gg * CSET;
-        const int kk = k0 + gg;
-        float v = 0.f;
-        if (kk >= 1 && kk < N) v = __ldg(P.C + (size_t)(kk - 1) * CSET + e);
-        if (e < SS) TA[(gg + 1) * TK + e] = v;                                   // column-major A
-        else { const int m = (e - SS) / S, i = (e - SS) - m * S; PW[(gg + 1) * PK + m * PR + cL + i] = v; }
+    // (float2 granularity: CSET, SS and S are even, so a pair never straddles a column; fixed
+    // trip count + unroll keeps 8 loads in flight per lane instead of one)
+    {
+        constexpr int TOT2 = KPC * CSET / 2, ITERS = (TOT2 + CF::NT - 1) / CF::NT;
+        const float2* src = reinterpret_cast<const float2*>(P.C + ((ptrdiff_t)k0 - 1) * CSET);
+#pragma unroll 8
+        for (int it = 0; it < ITERS; it++) {
+            const int i2 = tid + it * CF::NT;
+            if (i2 < TOT2) {
+                const int idx = 2 * i2;
+                const int gg = idx / CSET, e = idx - gg * CSET;
+                const int kk = k0 + gg;
+                float2 v = f2(0.f, 0.f);
+                if (kk >= 1 && kk < N) v = __ldg(src + i2);
+                if (e < SS) *reinterpret_cast<float2*>(TA + (gg + 1) * TK + e) = v;     // column-major A
+                else {
+                    const int m = (e - SS) / S, i = (e - SS) - m * S;
+                    *reinterpret_cast<float2*>(PW + (gg + 1) * PK + m * PR + cL + i) = v;
+                }
+            }
+        }
     }
     // halo knots: keep every tile that an edge knot may read finite
     for (int q = tid; q < 2 * PK; q += CF::NT) PW[(q < PK) ? q : (KPC + 1) * PK + (q - PK)] = 0.f;
