@@ -52,7 +52,8 @@ struct Cfg {
     static constexpr int NRED = CL * NW;                // partial sums per reduction
     static constexpr int NREDP = (NRED + 3) & ~3;
     static constexpr int oRed = oHal + 4 * VK;          // [2 bufs][NREDP]
-    static constexpr int FLOATS = oRed + 2 * NREDP;
+    static constexpr int oMb = oRed + 2 * NREDP;        // 2 mbarriers (8 B each), cluster kernels
+    static constexpr int FLOATS = oMb + 4;
     static constexpr size_t SMEM_BYTES = sizeof(float) * FLOATS;
     static constexpr int MIN_CTAS = (LPK == 4) ? 1 : (512 / NT > 0 ? 512 / NT : 1);
     static_assert(LPK == 4 || LPK == 8, "4 or 8 lanes per knot");
@@ -552,40 +553,56 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
 }
 
 // ---------------------------------------------------------------------------------------
-// Cluster-wide sum with a bit-identical result in every thread of every CTA: warp shuffle,
-// one (D)SMEM store per (warp, destination CTA), ONE barrier, then every thread adds the same
-// NRED partials in the same order.
+// Cluster-wide sum with a bit-identical result in every thread of every CTA.
+//  CL == 1: warp shuffle, one smem store per warp, __syncthreads, every thread adds the same
+//           NW partials in the same order.
+//  CL  > 1: every warp sends its partial to every CTA of the cluster with st.async (remote
+//           store + complete_tx on the destination's mbarrier); each CTA waits on its OWN
+//           mbarrier for NRED*4 (+ halo) bytes -- one-way DSMEM latency, no cluster barrier.
+//           All lanes then combine the same NRED partials with the same butterfly.
+// `mb` points at the two mbarriers (one per reduction kind), `par` at their phase parities.
 // ---------------------------------------------------------------------------------------
 template <class CF>
-__device__ __forceinline__ float cluster_sum(float* red, int buf, float val, unsigned rank) {
+__device__ __forceinline__ float cluster_sum(float* red, uint64_t* mb, unsigned (&par)[2], int buf,
+                                             float val, unsigned rank, unsigned halo_bytes) {
     constexpr int CL = CF::CL, NW = CF::NW, NRED = CF::NRED;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float w = warp_sum(val);
     float* slot = red + buf * CF::NREDP + rank * NW + warp;
     if constexpr (CL == 1) {
         if (lane == 0) *slot = w;
-    } else {
-        if (lane < CL) *map_rank<CL>(slot, (unsigned)lane) = w;
-    }
-    cluster_sync_all<CL>();
-    const float4* r4 = reinterpret_cast<const float4*>(red + buf * CF::NREDP);
-    float acc = 0.f;
+        __syncthreads();
+        const float4* r4 = reinterpret_cast<const float4*>(red + buf * CF::NREDP);
+        float acc = 0.f;
 #pragma unroll
-    for (int q = 0; q < CF::NREDP / 4; q++) {
-        const float4 v = r4[q];
-        acc += v.x;
-        if (4 * q + 1 < NRED) acc += v.y;
-        if (4 * q + 2 < NRED) acc += v.z;
-        if (4 * q + 3 < NRED) acc += v.w;
+        for (int q = 0; q < CF::NREDP / 4; q++) {
+            const float4 v = r4[q];
+            acc += v.x;
+            if (4 * q + 1 < NRED) acc += v.y;
+            if (4 * q + 2 < NRED) acc += v.z;
+            if (4 * q + 3 < NRED) acc += v.w;
+        }
+        return acc;
+    } else {
+        if (threadIdx.x == 0) mbar_arrive_expect_tx(mb + buf, (unsigned)NRED * 4u + halo_bytes);
+        if (lane < CL) st_async_f32(mapa_u32(smem_u32(slot), (unsigned)lane), w, mapa_u32(smem_u32(mb + buf), (unsigned)lane));
+        mbar_wait(mb + buf, par[buf]);
+        par[buf] ^= 1u;
+        float acc = 0.f;
+#pragma unroll
+        for (int q = 0; q < (NRED + 31) / 32; q++) {
+            const int idx = lane + 32 * q;
+            if (idx < NRED) acc += red[buf * CF::NREDP + idx];
+        }
+        return warp_sum(acc);
     }
-    return acc;
 }
 
 // ---------------------------------------------------------------------------------------
 // pcg_rows: preconditioned CG on the stored system S lambda = gamma.  Semantics (warm start,
 // |r.Pinv r| < tol absolute exit, iteration count, max-iter flag) follow SURVEY 0.2 /
-// oracle_pcg.  Per iteration: 2 reductions (one barrier each: __syncthreads for CL == 1, a
-// cluster barrier otherwise) + 2 CTA barriers; the boundary rows of S p and Pinv r ride
+// oracle_pcg.  Per iteration: 2 reductions (__syncthreads for CL == 1; st.async + mbarrier
+// across a cluster, no cluster-wide barrier) + 2 CTA barriers; the boundary rows of S p and Pinv r ride
 // along with the partial sums, so neighbouring CTAs update their halo copies of r and p
 // locally and need no further exchange.
 // ---------------------------------------------------------------------------------------
@@ -609,6 +626,10 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     float* rv = smem + CF::oRv;
     float* hal = smem + CF::oHal;   // [phase][side][16]; side 0: pushed by my LEFT neighbour CTA
     float* red = smem + CF::oRed;
+    uint64_t* mb = reinterpret_cast<uint64_t*>(smem + CF::oMb);
+    unsigned par[2] = {0u, 0u};
+    const unsigned hb = (CL > 1) ? ((has_l ? 56u : 0u) + (has_r ? 56u : 0u)) : 0u;   // halo bytes per phase
+    if (CL > 1 && tid == 0) { mbar_init(mb, 1); mbar_init(mb + 1, 1); fence_mbar_init_cluster(); }
     const float* myP = smem + CF::oP + sl * PK;
 
     // y(rows) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
@@ -650,6 +671,12 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     auto put = [&](float* dst, const float (&v)[RPT]) {        // my rows of a 16-float vector slot
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) dst[rm.row[j]] = v[j];
+    };
+    // my rows -> a 16-float slot of a neighbour CTA, completing bytes on ITS mbarrier `buf`
+    auto push = [&](float* local_dst, unsigned dst_rank, int buf, const float (&v)[RPT]) {
+        const uint32_t ra = mapa_u32(smem_u32(local_dst), dst_rank), rb = mapa_u32(smem_u32(mb + buf), dst_rank);
+#pragma unroll
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) st_async_f32(ra + 4u * rm.row[j], v[j], rb);
     };
     auto dotp = [&](const float (&a)[RPT], const float (&b)[RPT]) {
         float d = 0.f;
@@ -693,9 +720,9 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
 #pragma unroll
     for (int j = 0; j < RPT; j++) pp[j] = rt[j];
     put(pv + sl * VK, pp);                   // pv was last read before the barrier above
-    if (first_g) { if (has_l) put(map_rank<CL>(hr_p, rank - 1), pp); else put(hl_p, zero); }
-    if (last_g)  { if (has_r) put(map_rank<CL>(hl_p, rank + 1), pp); else put(hr_p, zero); }
-    float eta = cluster_sum<CF>(red, 1, dotp(rr, rt), rank);
+    if (first_g) { if (has_l) push(hr_p, rank - 1, 1, pp); else put(hl_p, zero); }
+    if (last_g)  { if (has_r) push(hl_p, rank + 1, 1, pp); else put(hr_p, zero); }
+    float eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
 
     unsigned iter = 0;
     bool max_iter_exit = true;
@@ -703,10 +730,10 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
         // ---- ups = S p ; v = p.ups -----------------------------------------------------------
         s_mv(pv, y);
         if (CL > 1) {
-            if (first_g && has_l) put(map_rank<CL>(hal + (0 * 2 + 1) * VK, rank - 1), y);
-            if (last_g && has_r)  put(map_rank<CL>(hal + (0 * 2 + 0) * VK, rank + 1), y);
+            if (first_g && has_l) push(hal + (0 * 2 + 1) * VK, rank - 1, 0, y);
+            if (last_g && has_r)  push(hal + (0 * 2 + 0) * VK, rank + 1, 0, y);
         }
-        const float v = cluster_sum<CF>(red, 0, dotp(pp, y), rank);
+        const float v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
         if (v == 0.f) { max_iter_exit = false; break; }
         const float alpha = eta / v;
 #pragma unroll
@@ -725,10 +752,10 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
         // ---- rt = Pinv r ; eta_new = r.rt ----------------------------------------------------
         p_mv(rv, rt);
         if (CL > 1) {
-            if (first_g && has_l) put(map_rank<CL>(hal + (1 * 2 + 1) * VK, rank - 1), rt);
-            if (last_g && has_r)  put(map_rank<CL>(hal + (1 * 2 + 0) * VK, rank + 1), rt);
+            if (first_g && has_l) push(hal + (1 * 2 + 1) * VK, rank - 1, 1, rt);
+            if (last_g && has_r)  push(hal + (1 * 2 + 0) * VK, rank + 1, 1, rt);
         }
-        const float eta_new = cluster_sum<CF>(red, 1, dotp(rr, rt), rank);
+        const float eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
         if (fabsf(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
         const float beta = eta_new / eta;
         eta = eta_new;
