@@ -35,4 +35,16 @@ with torch.cuda.stream(st):
     gr.replay(); torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(st); gr.replay(); e1.record(st); torch.cuda.synchronize()
-print("N", N, "iters", int(it.item()), "us per (memset+pcg)", e0.elapsed_time(e1) / 20 * 1e3)
+t_full = e0.elapsed_time(e1) / 20 * 1e3
+iters = int(it.item())
+cfg0 = mg.PcgConfig(pcg_exit_tol=1e-4, pcg_max_iter=0)
+with torch.cuda.stream(st):
+    g0 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g0, stream=st):
+        for _ in range(20):
+            lam.zero_()
+            mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg0)
+    g0.replay(); torch.cuda.synchronize()
+    e0.record(st); g0.replay(); e1.record(st); torch.cuda.synchronize()
+t0 = e0.elapsed_time(e1) / 20 * 1e3
+print("N %d iters %d  solve %.1f us  floor(max_iter=0) %.1f us  per-iter %.3f us" % (N, iters, t_full, t0, (t_full - t0) / max(iters, 1)))
