@@ -33,6 +33,56 @@ def _stale(out, srcs):
     return any(os.path.exists(s) and os.path.getmtime(s) > t for s in srcs)
 
 
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+RUN = os.path.join(REFOUT, "run")            # working directory of the reference executables
+HARNESS = os.path.join(RUN, "ref_harness")
+TRACK = os.path.join(RUN, "track_iiwa_pcg_n%d")
+TRACK_KNOTS = (32, 128)
+
+
+def _ref_nvcc(src, out, defs=()):
+    root = os.path.dirname(HERE)
+    inc = [os.path.join(root, "mpcgpu_b200", "shim"), os.path.join(root, "include"),
+           os.path.join(REF, "include"), os.path.join(REF, "include", "common"),
+           os.path.join(REF, "include", "pcg"), os.path.join(REF, "include", "dynamics"),
+           os.path.join(REF, "include", "utils"), os.path.join(REF, "qdldl", "include"),
+           os.path.join(HERE, "qdldl_cfg", "f32"), os.path.join(HERE, "qdldl_cfg")]
+    cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-w", "-lineinfo"]
+    cmd += list(defs) + [a for i in inc for a in ("-I", i)] + [src, "-o", out, "-lcublas"]
+    _run(cmd)
+
+
+def _build_reference_cuda(force, verbose):
+    """The reference's OWN CUDA code (its form_schur_system kernel, KKT generation with the
+    GRiD dynamics, and the whole examples/track_iiwa_pcg.cu tracking loop), compiled UNCHANGED
+    from /root/reference against the shim headers (mpcgpu_b200/shim stands in for the empty
+    GBD-PCG / GLASS submodules).  Outputs only under oracle/_ref/run/, which also receives a
+    copy of the two trajectory fixtures the executables read by relative path."""
+    if not os.path.exists(NVCC):
+        return
+    import glob
+    import shutil
+    root = os.path.dirname(HERE)
+    deps = glob.glob(os.path.join(root, "mpcgpu_b200", "shim", "*.cuh")) + \
+        glob.glob(os.path.join(root, "mpcgpu_b200", "csrc", "*.cuh")) + [os.path.join(HERE, "ref_harness.cu")]
+    os.makedirs(os.path.join(RUN, "examples", "trajfiles"), exist_ok=True)
+    os.makedirs(os.path.join(RUN, "tmp", "results"), exist_ok=True)
+    for f in ("0_0_eepos.traj", "0_0_traj.csv"):
+        dst = os.path.join(RUN, "examples", "trajfiles", f)
+        if not os.path.exists(dst):
+            shutil.copyfile(os.path.join(REF, "examples", "trajfiles", f), dst)
+    if force or _stale(HARNESS, deps):
+        _ref_nvcc(os.path.join(HERE, "ref_harness.cu"), HARNESS)
+        if verbose:
+            print("built", HARNESS)
+    for n in TRACK_KNOTS:
+        out = TRACK % n
+        if force or _stale(out, deps):
+            _ref_nvcc(os.path.join(REF, "examples", "track_iiwa_pcg.cu"), out, ["-DKNOT_POINTS=%d" % n])
+            if verbose:
+                print("built", out)
+
+
 def build(force=False, verbose=False):
     os.makedirs(BUILD, exist_ok=True)
     os.makedirs(REFOUT, exist_ok=True)
@@ -64,6 +114,7 @@ def build(force=False, verbose=False):
                   *i32, "-o", base, "cpu_baseline.c", "mpc_oracle.c", qsrc, "-lm"])
         if verbose:
             print("built", f32, f64, base)
+        _build_reference_cuda(force, verbose)
     else:
         missing = [p for p in (f32, f64, base) if not os.path.exists(p)]
         if missing:

@@ -1,0 +1,108 @@
+"""GPU tests (-m gpu) against the REFERENCE'S OWN CUDA CODE.
+
+oracle/_ref/run/ref_harness is compiled (oracle/build.py, in the build container) from the
+reference's unchanged headers -- its form_schur_system kernel (include/pcg/linsys_setup.cuh), its
+generate_kkt_submatrices with the GRiD IIWA dynamics (include/common/kkt.cuh) -- against the
+drop-in shim headers of mpcgpu_b200/shim.  The prebuilt binary travels to the GPU box; nothing
+here reads /root/reference at run time.
+
+  * real IIWA KKT blocks (G, C, g, c) from the reference's KKT kernel on the 0_0 trajectory
+  * S, Pinv, gamma, G^-1 from the reference's own Schur kernel  vs  our kernel  vs  the oracle
+  * the shim's pcg<float,14,N> launched exactly like include/pcg/sqp.cuh:275  vs  the oracle
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import mpcgpu_b200 as mg
+from helpers import S, C, rel, block_rel
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+RUN = os.path.join(ROOT, "oracle", "_ref", "run")
+HARNESS = os.path.join(RUN, "ref_harness")
+DEV = "cuda:0"
+
+
+def harness(*args):
+    if not os.path.exists(HARNESS):
+        pytest.fail("oracle/_ref/run/ref_harness missing: run oracle/build.py where /root/reference exists")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+    r = subprocess.run([HARNESS, *[str(a) for a in args]], cwd=RUN, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout[-500:], r.stderr[-500:])
+
+
+def split(buf, sizes):
+    out, o = [], 0
+    for n in sizes:
+        out.append(buf[o:o + n]); o += n
+    assert o == buf.size
+    return out
+
+
+def real_kkt(N, row0, perturb, tmp):
+    z = mg.sizes(S, C, N)
+    f = os.path.join(tmp, "kkt_%d_%d.bin" % (N, row0))
+    harness("kkt", N, row0, perturb, f)
+    G, Cm, g, cv = split(np.fromfile(f, np.float32), [z["G"], z["C"], z["g"], z["c"]])
+    return f, G, Cm, g, cv
+
+
+@pytest.mark.parametrize("N,row0,perturb", [(8, 0, 0.02), (32, 0, 0.02), (64, 100, 0.05), (128, 300, 0.02), (512, 0, 0.01)])
+def test_schur_matches_reference_kernel_on_real_iiwa_blocks(N, row0, perturb, tmp_path):
+    tmp = str(tmp_path)
+    z = mg.sizes(S, C, N)
+    rho = 1e-3
+    fin, G, Cm, g, cv = real_kkt(N, row0, perturb, tmp)
+    assert np.all(np.isfinite(G)) and np.all(np.isfinite(Cm)) and np.abs(cv[S:]).max() > 0
+    fout = os.path.join(tmp, "schur.bin")
+    harness("schur", N, rho, fin, fout)
+    Sr, Pr, gr, Gir = split(np.fromfile(fout, np.float32), [z["S"], z["S"], z["gamma"], z["G"]])
+    # ours
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(DEV)[None]
+    Gd = t(G).clone()
+    Sg = torch.full((1, z["S"]), float("nan"), device=DEV); Pg = torch.full_like(Sg, float("nan"))
+    gam = torch.full((1, z["gamma"]), float("nan"), device=DEV)
+    mg.form_schur_system(S, C, N, Gd, t(Cm), t(g), t(cv), Sg, Pg, gam, rho)
+    torch.cuda.synchronize()
+    So, Po, go, Gio = Sg[0].cpu().numpy(), Pg[0].cpu().numpy(), gam[0].cpu().numpy(), Gd[0].cpu().numpy()
+    # oracle (fp32 and fp64 restatement)
+    o32 = oracle.schur(S, C, N, G, Cm, g, cv, rho, np.float32)
+    o64 = oracle.schur(S, C, N, G, Cm, g, cv, rho, np.float64)
+    for name, (a, b) in {"ours-vs-reference": ((So, Po, go, Gio), (Sr, Pr, gr, Gir)),
+                         "oracle32-vs-reference": (o32, (Sr, Pr, gr, Gir)),
+                         "ours-vs-oracle64": ((So, Po, go, Gio), o64)}.items():
+        assert block_rel(S, N, a[0], b[0]) < 1e-4, name
+        assert block_rel(S, N, a[1], b[1]) < 1e-4, name
+        assert rel(a[2], b[2]) < 1e-4, name
+        assert rel(a[3], b[3]) < 1e-4, name
+    # keep the captured blocks + reference outputs (small cases become committed golden fixtures)
+    keep = os.path.join(ROOT, "gpurun_out")
+    if N <= 32 and os.path.isdir(keep):
+        np.savez_compressed(os.path.join(keep, "iiwa_kkt_n%d.npz" % N), N=N, row0=row0, perturb=perturb, rho=rho,
+                            G=G, C=Cm, g=g, cvec=cv, S_ref=Sr, Pinv_ref=Pr, gamma_ref=gr, Ginv_ref=Gir)
+
+
+@pytest.mark.parametrize("N,tol", [(8, 1e-6), (32, 1e-5), (64, 1e-4), (128, 1e-4), (512, 1e-4)])
+def test_shim_pcg_launched_like_the_reference_slot(N, tol, tmp_path):
+    """pcg<float,14,N> of mpcgpu_b200/shim/gpu_pcg.cuh behind the reference's launch
+    (cooperative, grid = N, 128 threads, pcgSharedMemSize; include/pcg/sqp.cuh:275-277)."""
+    tmp = str(tmp_path)
+    z = mg.sizes(S, C, N)
+    _, G, Cm, g, cv = real_kkt(N, 50, 0.03, tmp)
+    S32, P32, g32, _ = oracle.schur(S, C, N, G, Cm, g, cv, 1e-3, np.float32)
+    lam0 = np.zeros(S * N, np.float32)
+    fin, fout = os.path.join(tmp, "pcg_in.bin"), os.path.join(tmp, "pcg_out.bin")
+    np.concatenate([S32, P32, g32, lam0]).astype(np.float32).tofile(fin)
+    harness("pcg", N, tol, 10000, fin, fout)
+    o = np.fromfile(fout, np.float32)
+    lam_g, it_g, ex_g = o[:S * N], int(o[S * N]), bool(o[S * N + 1])
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S32, P32, g32, lam0, 10000, tol)
+    assert abs(it_g - it_o) <= 1 and ex_g == ex_o, (it_g, it_o)
+    lam_s, _, _ = oracle.pcg(S, N, S32, P32, g32, lam0, it_g, 0.0)
+    assert rel(lam_g, lam_s) < max(1e-4, 3.0 * oracle.pcg_noise_floor(S, N, S32, P32, g32, lam0, it_g))

@@ -217,3 +217,26 @@ def test_product_never_imports_oracle():
                 src = open(os.path.join(dp, f)).read()
                 assert "import oracle" not in src and "from oracle" not in src, f
                 assert "oracle/" not in src or f.endswith((".md",)), f
+
+
+# ---- fixtures produced by the REFERENCE'S OWN CUDA kernels on a B200 ------------------------------
+@pytest.mark.parametrize("name", ["iiwa_kkt_n8.npz", "iiwa_kkt_n32.npz"])
+def test_oracle_matches_reference_schur_kernel_outputs(name):
+    """tests/golden/iiwa_kkt_n*.npz: real IIWA KKT blocks from the reference's
+    generate_kkt_submatrices (GRiD dynamics, 0_0 trajectory) and the S / Pinv / gamma / G^-1 its
+    own form_schur_system kernel computed from them on a B200 (tests/test_gpu_reference.py wrote
+    them through oracle/_ref/run/ref_harness).  Pins the oracle's restatement to the reference."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", name))
+    N = int(z["N"])
+    for dtype in (np.float32, np.float64):
+        S_o, P_o, g_o, Gi_o = oracle.schur(S, C, N, z["G"], z["C"], z["g"], z["cvec"], float(z["rho"]), dtype)
+        assert block_rel(S, N, S_o, z["S_ref"]) < 1e-4
+        assert block_rel(S, N, P_o, z["Pinv_ref"]) < 1e-4
+        assert rel(g_o, z["gamma_ref"]) < 1e-4
+        assert rel(Gi_o, z["Ginv_ref"]) < 1e-4
+    # and the whole path: reference QDLDL on the reference kernel's S  vs  on the oracle's S
+    S64, _, g64, _ = oracle.schur(S, C, N, z["G"], z["C"], z["g"], z["cvec"], float(z["rho"]), np.float64)
+    lam_ref = oracle.qdldl_solve(S, N, z["S_ref"].astype(np.float64), z["gamma_ref"].astype(np.float64))
+    lam_o = oracle.qdldl_solve(S, N, S64, g64)
+    assert rel(oracle.bdmv(S, N, S64, lam_ref), g64) < 1e-3
+    assert np.all(np.isfinite(lam_o))
