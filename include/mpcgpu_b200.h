@@ -109,6 +109,29 @@ int mpcgpu_b200_solver_solve_host_f32(mpcgpu_b200_solver* solver, uint32_t batch
                                       uint32_t max_iter, float exit_tol, uint32_t* h_iters,
                                       uint8_t* h_max_iter_exit, float* h_Ginv);
 
+/* ---- long horizon split by knot range across the GPUs of one box (NEW: the reference has no
+ * multi-GPU path; BASELINE.json configs[3]).  Rank r owns knots
+ * [r*knots_local, (r+1)*knots_local) and holds only ITS slices of S / Pinv / gamma / lambda
+ * (block rows of the reference layout, include/pcg/sqp.cuh:111,130).  Per PCG iteration the
+ * boundary rows of S p and Pinv r and the two scalar sums travel as tagged 8-byte peer stores
+ * over NVLink into a mailbox in each destination GPU; there is no NCCL call and no kernel
+ * boundary inside the solve.  d_mailboxes: HOST array of `world` device pointers (this rank's
+ * own mailbox and the peers' mailboxes mapped with mpcgpu_b200_ipc_open), each
+ * mpcgpu_b200_knotsplit_mailbox_bytes() long and zeroed once.  `epoch` must be identical on
+ * all ranks and grow by more than 2*max_iter+8 from one solve to the next.
+ * ranks_here > 1 emulates several ranks in one cooperative launch on ONE GPU (tests). */
+size_t mpcgpu_b200_knotsplit_mailbox_bytes(void);
+int mpcgpu_b200_knotsplit_pcg_f32(uint32_t state_size, uint32_t knots_local, uint32_t ranks_here,
+                                  uint32_t rank_first, uint32_t world, uint32_t epoch,
+                                  void* const* d_mailboxes, const float* d_S, const float* d_Pinv,
+                                  const float* d_gamma, float* d_lambda, uint32_t max_iter,
+                                  float exit_tol, uint32_t* d_iters, uint8_t* d_max_iter_exit,
+                                  void* stream);
+/* CUDA IPC plumbing for the mailboxes (one process per GPU): 64-byte handle out / in. */
+int mpcgpu_b200_ipc_export(const void* d_ptr, void* handle64);
+int mpcgpu_b200_ipc_open(const void* handle64, void** d_ptr);
+int mpcgpu_b200_ipc_close(void* d_ptr);
+
 /* Kernel launches issued by this library since load (all threads). */
 uint64_t mpcgpu_b200_launch_count(void);
 

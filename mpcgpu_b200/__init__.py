@@ -7,8 +7,9 @@ reference interface over that ABI), shim/ (drop-in headers for the reference's o
 include/pcg/sqp.cuh), synth.py (seeded synthetic KKT blocks).
 """
 from . import synth  # noqa: F401
-from .api import (HostSolver, MpcGpuError, PcgConfig, form_schur_system, kkt_solve,  # noqa: F401
-                  launch_count, lib, pcg, sizes)
+from .api import (HostSolver, KnotSplitGroup, MpcGpuError, PcgConfig, epoch_stride,  # noqa: F401
+                  form_schur_system, kkt_solve, knot_range, knotsplit_pcg, launch_count, lib,
+                  mailbox_bytes, pcg, schur_slice, sizes)
 
 __all__ = ["HostSolver", "MpcGpuError", "PcgConfig", "form_schur_system", "kkt_solve", "pcg",
            "sizes", "synth", "lib", "launch_count"]

@@ -199,3 +199,94 @@ class HostSolver:
             self.close()
         except Exception:
             pass
+
+
+# ---- long horizon split by knot range across GPUs (BASELINE.json configs[3]) ----------------------
+def knot_range(knot_points, rank, world):
+    """Knots [lo, hi) owned by `rank`: equal contiguous ranges (the kernels need 16, 32, 64, 128,
+    256 or 512 knots per rank)."""
+    if knot_points % world:
+        raise MpcGpuError("knot_points %d not divisible by world %d" % (knot_points, world))
+    n = knot_points // world
+    if n not in (16, 32, 64, 128, 256, 512):
+        raise MpcGpuError("knots per rank must be 16..512 in powers of two, got %d" % n)
+    return rank * n, (rank + 1) * n
+
+
+def schur_slice(knot_points, rank, world):
+    """Extended knot range [lo, hi) a rank feeds to form_schur_system so that the S / Pinv /
+    gamma block rows of ITS knots come out exactly as in the full-horizon computation, with no
+    communication: two extra knots to the left (theta^-1 of knot lo-1 needs phi of lo-1, which
+    needs Q of lo-2) and one to the right (S-right / Pinv-right of the last owned knot).
+    Returns (lo_ext, hi_ext, offset of the first owned knot inside the slice)."""
+    lo, hi = knot_range(knot_points, rank, world)
+    lo_e, hi_e = max(lo - 2, 0), min(hi + 1, knot_points)
+    return lo_e, hi_e, lo - lo_e
+
+
+def mailbox_bytes():
+    lib().mpcgpu_b200_knotsplit_mailbox_bytes.restype = ctypes.c_size_t
+    return int(lib().mpcgpu_b200_knotsplit_mailbox_bytes())
+
+
+def knotsplit_pcg(state_size, knots_local, ranks_here, rank_first, world, epoch, mailboxes, d_S, d_Pinv,
+                  d_gamma, d_lambda, d_pcg_iters, d_pcg_exit, config: PcgConfig):
+    """PCG on a knot-range-split horizon.  `mailboxes`: `world` integers (device addresses of every
+    rank's mailbox as seen from THIS device).  d_S / d_Pinv / d_gamma / d_lambda hold the slices of
+    the `ranks_here` ranks resident on this device, in rank order (ranks_here > 1: single-GPU
+    emulation)."""
+    s, n, f = state_size, knots_local * ranks_here, torch.float32
+    arr = (ctypes.c_void_p * world)(*[ctypes.c_void_p(int(m)) for m in mailboxes])
+    rc = lib().mpcgpu_b200_knotsplit_pcg_f32(
+        ctypes.c_uint32(s), ctypes.c_uint32(knots_local), ctypes.c_uint32(ranks_here),
+        ctypes.c_uint32(rank_first), ctypes.c_uint32(world), ctypes.c_uint32(epoch), arr,
+        _ptr(d_S, f, "d_S", 3 * s * s * n), _ptr(d_Pinv, f, "d_Pinv", 3 * s * s * n),
+        _ptr(d_gamma, f, "d_gamma", s * n), _ptr(d_lambda, f, "d_lambda", s * n),
+        ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+        _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", ranks_here),
+        _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", ranks_here), _stream())
+    _check(rc, "knotsplit_pcg")
+
+
+def epoch_stride(config: PcgConfig):
+    return 2 * int(config.pcg_max_iter) + 16
+
+
+class KnotSplitGroup:
+    """One process per GPU (torch.distributed initialised): allocates this rank's mailbox, maps
+    the peers' mailboxes through CUDA IPC and keeps the solve epoch in step on all ranks."""
+
+    def __init__(self, group=None):
+        import torch.distributed as dist
+        self.dist, self.group = dist, group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.mail = torch.zeros(mailbox_bytes() // 4, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        h = (ctypes.c_ubyte * 64)()
+        _check(lib().mpcgpu_b200_ipc_export(ctypes.c_void_p(self.mail.data_ptr()), h), "ipc_export")
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(h), group=group)
+        self.ptrs, self._opened = [], []
+        for r, hb in enumerate(handles):
+            if r == self.rank:
+                self.ptrs.append(self.mail.data_ptr())
+            else:
+                p = ctypes.c_void_p()
+                buf = (ctypes.c_ubyte * 64).from_buffer_copy(hb)
+                _check(lib().mpcgpu_b200_ipc_open(buf, ctypes.byref(p)), "ipc_open")
+                self.ptrs.append(p.value)
+                self._opened.append(p)
+        self.epoch = 0
+        dist.barrier(group=group)
+
+    def pcg(self, state_size, knots_local, d_S, d_Pinv, d_gamma, d_lambda, d_iters, d_exit, config):
+        knotsplit_pcg(state_size, knots_local, 1, self.rank, self.world, self.epoch, self.ptrs, d_S, d_Pinv,
+                      d_gamma, d_lambda, d_iters, d_exit, config)
+        self.epoch += epoch_stride(config)
+
+    def close(self):
+        torch.cuda.synchronize()
+        self.dist.barrier(group=self.group)
+        for p in self._opened:
+            lib().mpcgpu_b200_ipc_close(p)
+        self._opened = []

@@ -213,3 +213,101 @@ int mpcgpu_b200_pcg_refstyle_f32(uint32_t s, uint32_t N, const float* d_S, const
 }
 
 }  // extern "C"
+
+// ---- knot-range split (configs[3]) ------------------------------------------------------------
+namespace {
+template <class CF>
+cudaError_t launch_split(const SplitArgs& a, int ranks_here, cudaStream_t st) {
+    auto kern = pcg_split_kernel<CF>;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (configured_dev != dev) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        if (CF::CL > 8) {
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            if (e != cudaSuccess) return e;
+        }
+        configured_dev = dev;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)ranks_here * CF::CL, 1, 1);
+    cfg.blockDim = dim3(CF::NT, 1, 1);
+    cfg.dynamicSmemBytes = CF::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CF::CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (ranks_here > 1) {   // emulated ranks wait on one another: they must be co-resident
+        attr[1].id = cudaLaunchAttributeCooperative;
+        attr[1].val.cooperative = 1;
+        cfg.numAttrs = 2;
+    }
+    e = cudaLaunchKernelEx(&cfg, kern, a);
+    if (e == cudaSuccess) g_launches.fetch_add(1, std::memory_order_relaxed);
+    return e;
+}
+}  // namespace
+
+extern "C" {
+
+size_t mpcgpu_b200_knotsplit_mailbox_bytes(void) { return sizeof(uint2) * SPLIT_MAIL_U2; }
+
+int mpcgpu_b200_ipc_export(const void* d_ptr, void* handle64) {
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr));
+    if (e != cudaSuccess) return fail(e, "mpcgpu_b200_ipc_export");
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+
+int mpcgpu_b200_ipc_open(const void* handle64, void** d_ptr) {
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    cudaError_t e = cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_ipc_open");
+}
+
+int mpcgpu_b200_ipc_close(void* d_ptr) {
+    cudaError_t e = cudaIpcCloseMemHandle(d_ptr);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_ipc_close");
+}
+
+int mpcgpu_b200_knotsplit_pcg_f32(uint32_t s, uint32_t knots_local, uint32_t ranks_here, uint32_t rank_first,
+                                  uint32_t world, uint32_t epoch, void* const* d_mailboxes, const float* d_S,
+                                  const float* d_Pinv, const float* d_gamma, float* d_lambda, uint32_t max_iter,
+                                  float exit_tol, uint32_t* d_iters, uint8_t* d_max_iter_exit, void* stream) {
+    if (s != 14 || world < 1 || world > SPLIT_MAXW || ranks_here < 1 || rank_first + ranks_here > world)
+        return bad("mpcgpu_b200_knotsplit_pcg_f32: need s=14, 1 <= world <= 16, rank_first + ranks_here <= world");
+    if (!d_mailboxes || !d_S || !d_Pinv || !d_gamma || !d_lambda || !d_iters || !d_max_iter_exit)
+        return bad("mpcgpu_b200_knotsplit_pcg_f32: null pointer");
+    SplitArgs a;
+    memset(&a, 0, sizeof(a));
+    a.n_local = (int)knots_local; a.grank_first = rank_first; a.world = world; a.epoch = epoch;
+    for (uint32_t r = 0; r < world; r++) {
+        if (!d_mailboxes[r]) return bad("mpcgpu_b200_knotsplit_pcg_f32: null mailbox");
+        a.mail[r] = (uint2*)d_mailboxes[r];
+    }
+    a.S = d_S; a.Pinv = d_Pinv; a.gamma = d_gamma; a.lambda = d_lambda;
+    a.max_iter = max_iter; a.exit_tol = exit_tol; a.iters = d_iters; a.exits = d_max_iter_exit;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaError_t e;
+    switch (knots_local) {
+        case 16: e = launch_split<Cfg<16, 1, 8>>(a, (int)ranks_here, st); break;
+        case 32: e = launch_split<Cfg<16, 2, 8>>(a, (int)ranks_here, st); break;
+        case 64: e = launch_split<Cfg<16, 4, 8>>(a, (int)ranks_here, st); break;
+        case 128: e = launch_split<Cfg<16, 8, 8>>(a, (int)ranks_here, st); break;
+        case 256: e = launch_split<Cfg<16, 16, 8>>(a, (int)ranks_here, st); break;
+        case 512: e = launch_split<Cfg<32, 16, 8>>(a, (int)ranks_here, st); break;
+        default: return bad("mpcgpu_b200_knotsplit_pcg_f32: knots per rank must be 16, 32, 64, 128, 256 or 512");
+    }
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_knotsplit_pcg_f32");
+}
+
+}  // extern "C"

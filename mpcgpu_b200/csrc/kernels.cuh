@@ -64,7 +64,10 @@ __device__ __forceinline__ void store_rows(const float* smem, const Rows<CF::RPT
 template <class CF>
 __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const float* __restrict__ Sg,
                                           const float* __restrict__ Pg,
-                                          const float* __restrict__ gam, int N) {
+                                          const float* __restrict__ gam, int N,
+                                          bool glob_l = false, bool glob_r = false) {
+    // glob_l / glob_r: this cluster's first / last knot has a neighbour on ANOTHER rank (knot-range
+    // split), so its left / right blocks are real data, not the never-written corner blocks
     constexpr int S = 14, SS = S * S;
     const int g = threadIdx.x / CF::LPK, t = threadIdx.x % CF::LPK;
     const int k0 = cluster_rank<CF::CL>() * CF::KPC;
@@ -74,7 +77,7 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
 #pragma unroll
     for (int j = 0; j < CF::RPT; j++) {
         const bool on = (k < N) && rm.ok[j];
-        const bool hl = on && k > 0, hr = on && (k + 1 < N);
+        const bool hl = on && (k > 0 || glob_l), hr = on && (k + 1 < N || glob_r);
         const int r = rm.row[j];
 #pragma unroll
         for (int c = 0; c < S; c++) {
@@ -95,7 +98,7 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
                 const int gg = e / (3 * SS), w = e - gg * 3 * SS;
                 const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
                 const int kk = k0 + gg;
-                const bool corner = (kk == 0 && blk == 0) || (kk == N - 1 && blk == 2);
+                const bool corner = (kk == 0 && blk == 0 && !glob_l) || (kk == N - 1 && blk == 2 && !glob_r);
                 float2 v = make_float2(0.f, 0.f);
                 if (kk < N && !corner) v = __ldg(src + e2);
                 float* d = smem + CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j;
@@ -145,6 +148,33 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a
     schur_rows<CF>(smem, P, a.N, a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
+}
+
+// ---- knot-range split across GPUs (BASELINE.json configs[3]) -----------------------------------
+// One cluster per RANK.  A real multi-GPU run launches one cluster per process/GPU; the
+// single-GPU emulation used by the tests launches `ranks_here` clusters in ONE (cooperative)
+// launch over all ranks' data -- the same code path with every mailbox local.
+struct SplitArgs {
+    int n_local;                 // knots per rank (== KPC * CL)
+    unsigned grank_first, world, epoch;
+    uint2* mail[SPLIT_MAXW];     // mailbox of every rank (local or peer-mapped)
+    const float* S; const float* Pinv; const float* gamma; float* lambda;   // first local rank's slices
+    unsigned max_iter; float exit_tol;
+    unsigned* iters; uint8_t* exits;   // one entry per local rank
+};
+
+template <class CF>
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_split_kernel(SplitArgs a) {
+    extern __shared__ float4 smem4[];
+    float* smem = reinterpret_cast<float*>(smem4);
+    const int c = blockIdx.x / CF::CL;                  // local rank index within this launch
+    SplitCtx X{a.grank_first + (unsigned)c, a.world, a.epoch, a.mail};
+    const size_t ks = (size_t)c * a.n_local;
+    Rows<CF::RPT> R;
+    load_rows<CF>(smem, R, a.S + ks * 3 * 196, a.Pinv + ks * 3 * 196, a.gamma + ks * 14, a.n_local,
+                  X.grank > 0, X.grank + 1 < X.world);
+    pcg_rows<CF, true>(smem, R, a.lambda + ks * 14, a.n_local, a.max_iter, a.exit_tol, a.iters + c,
+                       a.exits + c, &X);
 }
 
 }  // namespace mpcb200

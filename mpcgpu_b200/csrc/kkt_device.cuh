@@ -599,6 +599,39 @@ __device__ __forceinline__ float cluster_sum(float* red, uint64_t* mb, unsigned 
 }
 
 // ---------------------------------------------------------------------------------------
+// Knot-range split across GPUs (BASELINE.json configs[3]): every rank (one GPU, one cluster)
+// owns a contiguous knot range; the block-tridiagonal coupling needs, per PCG iteration, the
+// boundary rows of S p / Pinv r from the two neighbour ranks and two scalar all-reduces.
+// Both travel as {value, tag} 8-byte system-scope stores into a small MAILBOX in the
+// destination GPU's memory (NVLink peer stores) and are consumed by polling the LOCAL mailbox:
+// no host round trip, no NCCL call, no kernel boundary per iteration.  Tags are
+// epoch + exchange counter, so a mailbox never needs clearing between solves.
+// Mailbox layout (uint2 units): red[2 bufs][16 ranks] | hal[5 phases][2 sides][16 rows].
+// ---------------------------------------------------------------------------------------
+constexpr int SPLIT_MAXW = 16;
+constexpr int SPLIT_HAL0 = 2 * SPLIT_MAXW;
+constexpr int SPLIT_MAIL_U2 = SPLIT_HAL0 + 5 * 2 * 16;      // 192 x 8 B
+struct SplitCtx {
+    unsigned grank, world;     // this cluster's rank among the knot-range owners
+    unsigned epoch;            // tag base of this solve (identical on all ranks, above all earlier tags)
+    uint2* const* mail;        // [world] mailbox of every rank (local or peer-mapped device pointers)
+};
+__device__ __forceinline__ void sys_store_tagged(uint2* dst, float v, unsigned tag) {
+    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(dst), "r"(__float_as_uint(v)), "r"(tag) : "memory");
+}
+// bounded spin: a dead peer must not hang the GPU -- after ~seconds the kernel traps (a loud
+// CUDA error on this rank) instead of waiting forever
+__device__ __forceinline__ float sys_poll_tagged(const uint2* src, unsigned tag) {
+    for (unsigned spin = 0; spin < (1u << 23); spin++) {
+        unsigned a, b;
+        asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(src) : "memory");
+        if (b == tag) return __uint_as_float(a);
+    }
+    __trap();
+    return 0.f;
+}
+
+// ---------------------------------------------------------------------------------------
 // pcg_rows: preconditioned CG on the stored system S lambda = gamma.  Semantics (warm start,
 // |r.Pinv r| < tol absolute exit, iteration count, max-iter flag) follow SURVEY 0.2 /
 // oracle_pcg.  Per iteration: 2 reductions (__syncthreads for CL == 1; st.async + mbarrier
@@ -606,10 +639,10 @@ __device__ __forceinline__ float cluster_sum(float* red, uint64_t* mb, unsigned 
 // along with the partial sums, so neighbouring CTAs update their halo copies of r and p
 // locally and need no further exchange.
 // ---------------------------------------------------------------------------------------
-template <class CF>
+template <class CF, bool SPLIT = false>
 __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, float* lam_g, int N,
                                          unsigned max_iter, float exit_tol, unsigned* d_iters,
-                                         uint8_t* d_exit) {
+                                         uint8_t* d_exit, const SplitCtx* X = nullptr) {
     constexpr int S = 14, KPC = CF::KPC, CL = CF::CL, PR = CF::PR, PK = CF::PK, VK = CF::VK;
     constexpr int LPK = CF::LPK, RPT = CF::RPT;
     const int tid = threadIdx.x;
@@ -620,6 +653,10 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     const RowMap<LPK, RPT, 14> rm(t);
     const bool first_g = (g == 0), last_g = (g == KPC - 1);
     const bool has_l = rank > 0, has_r = rank + 1 < (unsigned)CL;
+    // knot-range split: neighbours of the cluster's outer CTAs live on other GPUs
+    const bool gl = SPLIT && rank == 0 && X->grank > 0;
+    const bool gr = SPLIT && rank + 1 == (unsigned)CL && X->grank + 1 < X->world;
+    unsigned gseq[2] = {SPLIT ? X->epoch : 0u, SPLIT ? X->epoch : 0u};
     const int sl = g + 1;
 
     float* pv = smem + CF::oPv;
@@ -678,6 +715,34 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) st_async_f32(ra + 4u * rm.row[j], v[j], rb);
     };
+    // my rows -> mailbox [phase][side] of rank `dst` (another GPU), tagged
+    auto gpush = [&](int phase, int side, unsigned dst, unsigned tag, const float (&v)[RPT]) {
+        uint2* m = X->mail[dst] + SPLIT_HAL0 + (phase * 2 + side) * 16;
+#pragma unroll
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) sys_store_tagged(m + rm.row[j], v[j], tag);
+    };
+    auto gpull = [&](int phase, int side, int r, unsigned tag) {
+        return sys_poll_tagged(X->mail[X->grank] + SPLIT_HAL0 + (phase * 2 + side) * 16 + r, tag);
+    };
+    // boundary rows of the neighbour RANKS -> my halo slots (pre-loop exchanges, phases 2..4)
+    auto gpull_rows = [&](int phase, unsigned tag, float* left_slot, float* right_slot) {
+#pragma unroll
+        for (int j = 0; j < RPT; j++) {
+            if (!rm.ok[j]) continue;
+            const int r = rm.row[j];
+            if (first_g && gl) left_slot[r] = gpull(phase, 0, r, tag);
+            if (last_g && gr)  right_slot[r] = gpull(phase, 1, r, tag);
+        }
+    };
+    // all-reduce of the per-rank totals (w is already identical in every thread of this cluster)
+    auto gsum = [&](int buf, unsigned tag, float w) {
+        if (rank == 0 && tid < (int)X->world) sys_store_tagged(X->mail[tid] + buf * SPLIT_MAXW + X->grank, w, tag);
+        const int lane = tid & 31;
+        float v = 0.f;
+        if (lane < (int)X->world) v = sys_poll_tagged(X->mail[X->grank] + buf * SPLIT_MAXW + lane, tag);
+        __syncwarp();
+        return warp_sum(v);
+    };
     auto dotp = [&](const float (&a)[RPT], const float (&b)[RPT]) {
         float d = 0.f;
 #pragma unroll
@@ -706,13 +771,20 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) hr_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 + KPC) * S + rm.row[j]] : 0.f;
     }
+    const unsigned tg0 = SPLIT ? X->epoch + 1u : 0u;     // tag of the three pre-loop exchanges
+    if (SPLIT) {                                         // warm-start rows of the neighbour ranks
+        if (first_g && gl) gpush(2, 1, X->grank - 1, tg0, lam);
+        if (last_g && gr)  gpush(2, 0, X->grank + 1, tg0, lam);
+        gpull_rows(2, tg0, hl_p, hr_p);
+    }
     __syncthreads();
     s_mv(pv, y);
 #pragma unroll
     for (int j = 0; j < RPT; j++) rr[j] = rm.ok[j] ? R.gamma[j] - y[j] : 0.f;
     put(rv + sl * VK, rr);
-    if (first_g) { if (has_l) put(map_rank<CL>(hr_r, rank - 1), rr); else put(hl_r, zero); }
-    if (last_g)  { if (has_r) put(map_rank<CL>(hl_r, rank + 1), rr); else put(hr_r, zero); }
+    if (first_g) { if (has_l) put(map_rank<CL>(hr_r, rank - 1), rr); else if (gl) gpush(3, 1, X->grank - 1, tg0, rr); else put(hl_r, zero); }
+    if (last_g)  { if (has_r) put(map_rank<CL>(hl_r, rank + 1), rr); else if (gr) gpush(3, 0, X->grank + 1, tg0, rr); else put(hr_r, zero); }
+    if (SPLIT) gpull_rows(3, tg0, hl_r, hr_r);
     cluster_sync_all<CL>();
 
     // ---- p = rt = Pinv r ; eta = r.rt ----------------------------------------------------------
@@ -720,9 +792,11 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
 #pragma unroll
     for (int j = 0; j < RPT; j++) pp[j] = rt[j];
     put(pv + sl * VK, pp);                   // pv was last read before the barrier above
-    if (first_g) { if (has_l) push(hr_p, rank - 1, 1, pp); else put(hl_p, zero); }
-    if (last_g)  { if (has_r) push(hl_p, rank + 1, 1, pp); else put(hr_p, zero); }
+    if (first_g) { if (has_l) push(hr_p, rank - 1, 1, pp); else if (gl) gpush(4, 1, X->grank - 1, tg0, pp); else put(hl_p, zero); }
+    if (last_g)  { if (has_r) push(hl_p, rank + 1, 1, pp); else if (gr) gpush(4, 0, X->grank + 1, tg0, pp); else put(hr_p, zero); }
+    if (SPLIT) gpull_rows(4, tg0, hl_p, hr_p);
     float eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+    if (SPLIT) { eta = gsum(1, ++gseq[1], eta); __syncthreads(); }
 
     unsigned iter = 0;
     bool max_iter_exit = true;
@@ -733,7 +807,12 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             if (first_g && has_l) push(hal + (0 * 2 + 1) * VK, rank - 1, 0, y);
             if (last_g && has_r)  push(hal + (0 * 2 + 0) * VK, rank + 1, 0, y);
         }
-        const float v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
+        if (SPLIT) {
+            if (first_g && gl) gpush(0, 1, X->grank - 1, gseq[0] + 1, y);
+            if (last_g && gr)  gpush(0, 0, X->grank + 1, gseq[0] + 1, y);
+        }
+        float v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
+        if (SPLIT) v = gsum(0, ++gseq[0], v);
         if (v == 0.f) { max_iter_exit = false; break; }
         const float alpha = eta / v;
 #pragma unroll
@@ -748,6 +827,15 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
                 if (last_g && has_r)  hr_r[r] = fmaf(-alpha, hal[(0 * 2 + 1) * VK + r], hr_r[r]);
             }
         }
+        if (SPLIT) {
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                if (!rm.ok[j]) continue;
+                const int r = rm.row[j];
+                if (first_g && gl) hl_r[r] = fmaf(-alpha, gpull(0, 0, r, gseq[0]), hl_r[r]);
+                if (last_g && gr)  hr_r[r] = fmaf(-alpha, gpull(0, 1, r, gseq[0]), hr_r[r]);
+            }
+        }
         __syncthreads();
         // ---- rt = Pinv r ; eta_new = r.rt ----------------------------------------------------
         p_mv(rv, rt);
@@ -755,7 +843,12 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             if (first_g && has_l) push(hal + (1 * 2 + 1) * VK, rank - 1, 1, rt);
             if (last_g && has_r)  push(hal + (1 * 2 + 0) * VK, rank + 1, 1, rt);
         }
-        const float eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+        if (SPLIT) {
+            if (first_g && gl) gpush(1, 1, X->grank - 1, gseq[1] + 1, rt);
+            if (last_g && gr)  gpush(1, 0, X->grank + 1, gseq[1] + 1, rt);
+        }
+        float eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+        if (SPLIT) eta_new = gsum(1, ++gseq[1], eta_new);
         if (fabsf(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
         const float beta = eta_new / eta;
         eta = eta_new;
@@ -769,6 +862,15 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
                 const int r = rm.row[j];
                 if (first_g && has_l) hl_p[r] = fmaf(beta, hl_p[r], hal[(1 * 2 + 0) * VK + r]);
                 if (last_g && has_r)  hr_p[r] = fmaf(beta, hr_p[r], hal[(1 * 2 + 1) * VK + r]);
+            }
+        }
+        if (SPLIT) {
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                if (!rm.ok[j]) continue;
+                const int r = rm.row[j];
+                if (first_g && gl) hl_p[r] = fmaf(beta, hl_p[r], gpull(1, 0, r, gseq[1]));
+                if (last_g && gr)  hr_p[r] = fmaf(beta, hr_p[r], gpull(1, 1, r, gseq[1]));
             }
         }
         __syncthreads();
