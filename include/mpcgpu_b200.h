@@ -121,6 +121,9 @@ int mpcgpu_b200_solver_solve_host_f32(mpcgpu_b200_solver* solver, uint32_t batch
  * all ranks and grow by more than 2*max_iter+8 from one solve to the next.
  * ranks_here > 1 emulates several ranks in one cooperative launch on ONE GPU (tests). */
 size_t mpcgpu_b200_knotsplit_mailbox_bytes(void);
+/* a zeroed mailbox in its OWN cudaMalloc allocation (an IPC handle names a whole allocation) */
+int mpcgpu_b200_knotsplit_mailbox_create(void** d_mailbox);
+int mpcgpu_b200_knotsplit_mailbox_destroy(void* d_mailbox);
 int mpcgpu_b200_knotsplit_pcg_f32(uint32_t state_size, uint32_t knots_local, uint32_t ranks_here,
                                   uint32_t rank_first, uint32_t world, uint32_t epoch,
                                   void* const* d_mailboxes, const float* d_S, const float* d_Pinv,

@@ -260,16 +260,16 @@ class KnotSplitGroup:
         import torch.distributed as dist
         self.dist, self.group = dist, group
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
-        self.mail = torch.zeros(mailbox_bytes() // 4, dtype=torch.int32, device="cuda")
-        torch.cuda.synchronize()
+        self._mail = ctypes.c_void_p()
+        _check(lib().mpcgpu_b200_knotsplit_mailbox_create(ctypes.byref(self._mail)), "mailbox_create")
         h = (ctypes.c_ubyte * 64)()
-        _check(lib().mpcgpu_b200_ipc_export(ctypes.c_void_p(self.mail.data_ptr()), h), "ipc_export")
+        _check(lib().mpcgpu_b200_ipc_export(self._mail, h), "ipc_export")
         handles = [None] * self.world
         dist.all_gather_object(handles, bytes(h), group=group)
         self.ptrs, self._opened = [], []
         for r, hb in enumerate(handles):
             if r == self.rank:
-                self.ptrs.append(self.mail.data_ptr())
+                self.ptrs.append(self._mail.value)
             else:
                 p = ctypes.c_void_p()
                 buf = (ctypes.c_ubyte * 64).from_buffer_copy(hb)
@@ -290,3 +290,7 @@ class KnotSplitGroup:
         for p in self._opened:
             lib().mpcgpu_b200_ipc_close(p)
         self._opened = []
+        self.dist.barrier(group=self.group)
+        if self._mail:
+            lib().mpcgpu_b200_knotsplit_mailbox_destroy(self._mail)
+            self._mail = ctypes.c_void_p()

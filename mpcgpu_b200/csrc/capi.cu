@@ -258,6 +258,20 @@ extern "C" {
 
 size_t mpcgpu_b200_knotsplit_mailbox_bytes(void) { return sizeof(uint2) * SPLIT_MAIL_U2; }
 
+int mpcgpu_b200_knotsplit_mailbox_create(void** d_mailbox) {
+    // a dedicated cudaMalloc allocation: an IPC handle always names a whole allocation, so the
+    // mailbox must not be carved out of a caching allocator's segment
+    cudaError_t e = cudaMalloc(d_mailbox, sizeof(uint2) * SPLIT_MAIL_U2);
+    if (e == cudaSuccess) e = cudaMemset(*d_mailbox, 0, sizeof(uint2) * SPLIT_MAIL_U2);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_knotsplit_mailbox_create");
+}
+
+int mpcgpu_b200_knotsplit_mailbox_destroy(void* d_mailbox) {
+    cudaError_t e = cudaFree(d_mailbox);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_knotsplit_mailbox_destroy");
+}
+
 int mpcgpu_b200_ipc_export(const void* d_ptr, void* handle64) {
     cudaIpcMemHandle_t h;
     cudaError_t e = cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr));
