@@ -102,11 +102,28 @@ def cpu_reference_run(N, sample, steps, warmup, threads):
             "schur_share": float(np.mean([t[1] / (t[1] + t[2]) for t in times]))}
 
 
-def single_solve_latency(torch, mg, N, tol, reps=200):
-    """Single-instance latency (BASELINE.json metric (i)): PCG-only (cluster kernel vs the
-    reference-style 4-grid-barrier kernel), Schur-only and the fused solve; CUDA events around
-    `reps` back-to-back launches (inputs re-staged by D2D copies outside the kernel but inside
-    the events: negligible, 62 KB)."""
+def _graph_time_us(torch, fn, reset, reps=20):
+    """GPU-bound latency: a CUDA graph of `reps` (reset + fn) pairs replayed between two events on
+    its own stream, so that no host launch overhead sits between the kernels."""
+    st = torch.cuda.Stream()
+    with torch.cuda.stream(st):
+        for _ in range(3):
+            reset(); fn()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr, stream=st):
+            for _ in range(reps):
+                reset(); fn()
+        gr.replay(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(st); gr.replay(); e1.record(st); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps * 1e3
+
+
+def single_solve_latency(torch, mg, N, tol):
+    """Single-instance latency (BASELINE.json metric (i)), GPU-bound (CUDA-graph replay): PCG only
+    (cluster kernel vs the reference-STYLE 4-grid-barrier kernel, our restatement of the absent
+    GBD-PCG structure), Schur only, the fused solve, and the floor = same PCG launch with
+    max_iter = 0 (launch + load of S / Pinv + first residual)."""
     from mpcgpu_b200 import synth
     dev = "cuda"
     d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + N)
@@ -120,41 +137,64 @@ def single_solve_latency(torch, mg, N, tol, reps=200):
     lam = torch.zeros((1, S * N), device=dev)
     it = torch.zeros(1, dtype=torch.int32, device=dev); ex = torch.zeros(1, dtype=torch.uint8, device=dev)
     cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    cfg0 = mg.PcgConfig(pcg_exit_tol=tol, pcg_max_iter=0)
     ws = torch.empty(2 * S * N + 2 * N + 16, device=dev)
-
-    def timed(fn, reset):
-        for _ in range(10):
-            reset(); fn()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        tot = 0.0
-        for _ in range(reps):
-            reset()
-            e0.record(); fn(); e1.record()
-            e1.synchronize()
-            tot += e0.elapsed_time(e1)
-        return tot / reps * 1e3   # us
-
-    out = {"N": N, "tol": tol}
-    out["pcg_us"] = timed(lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg), lambda: lam.zero_())
+    out = {"N": N, "tol": tol, "timing": "CUDA-graph replay of 20 (memset + kernel) pairs, CUDA events"}
+    out["pcg_us"] = _graph_time_us(torch, lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg), lambda: lam.zero_())
     out["pcg_iters"] = int(it.item())
+    out["pcg_floor_us"] = _graph_time_us(torch, lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg0), lambda: lam.zero_())
+    out["pcg_us_per_iter"] = (out["pcg_us"] - out["pcg_floor_us"]) / max(out["pcg_iters"], 1)
     try:
-        out["pcg_refstyle_us"] = timed(lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg, refstyle=True, d_ws=ws),
-                                       lambda: lam.zero_())
+        out["pcg_refstyle_us"] = _graph_time_us(
+            torch, lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg, refstyle=True, d_ws=ws), lambda: lam.zero_())
         out["pcg_refstyle_iters"] = int(it.item())
-    except Exception as e:  # cooperative co-residency (N > resident CTAs) can refuse
+    except Exception as e:  # cooperative launches may refuse stream capture / co-residency
         out["pcg_refstyle_us"] = None
         out["pcg_refstyle_error"] = str(e)[:80]
-    out["schur_us"] = timed(lambda: mg.form_schur_system(S, C, N, G, Cm, g, cv, Sg, Pg, gam, d["rho"]),
-                            lambda: G.copy_(G0))
+    out["schur_us"] = _graph_time_us(torch, lambda: mg.form_schur_system(S, C, N, G, Cm, g, cv, Sg, Pg, gam, d["rho"]),
+                                     lambda: G.copy_(G0))
     def reset_f():
         G.copy_(G0); lam.zero_()
-    out["fused_us"] = timed(lambda: mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg), reset_f)
+    out["fused_us"] = _graph_time_us(torch, lambda: mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg), reset_f)
     out["fused_iters"] = int(it.item())
-    # launch floor: an empty-ish launch of the same geometry = pcg with max_iter 0
-    cfg0 = mg.PcgConfig(pcg_exit_tol=tol, pcg_max_iter=0)
-    out["launch_floor_us"] = timed(lambda: mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg0), lambda: None)
     return out
+
+
+def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, reps=30):
+    """BASELINE.json configs[3]: one N-knot horizon split by knot range over the `world` GPUs
+    (NVLink peer mailboxes, no collective call inside the solve).  Stream-timed, max over ranks."""
+    from mpcgpu_b200 import synth
+    d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + N)
+    lo, hi = mg.knot_range(N, rank, world)
+    lo_e, hi_e, off = mg.schur_slice(N, rank, world)
+    ne, n = hi_e - lo_e, hi - lo
+    ze = mg.sizes(S, C, ne)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)[None]
+    G = t(d["G"][0][lo_e * 245: lo_e * 245 + ze["G"]]); Cm = t(d["C"][0][lo_e * 294: lo_e * 294 + ze["C"]])
+    g = t(d["g"][0][lo_e * 21: lo_e * 21 + ze["g"]]); cv = t(d["c"][0][lo_e * 14: lo_e * 14 + ze["c"]])
+    Se = torch.empty((1, ze["S"]), device=dev); Pe = torch.empty_like(Se); ge = torch.empty((1, ze["gamma"]), device=dev)
+    mg.form_schur_system(S, C, ne, G, Cm, g, cv, Se, Pe, ge, d["rho"])
+    Sl = Se[0, off * 588:(off + n) * 588].contiguous(); Pl = Pe[0, off * 588:(off + n) * 588].contiguous()
+    gl = ge[0, off * 14:(off + n) * 14].contiguous()
+    lam = torch.zeros(n * 14, device=dev)
+    it = torch.zeros(1, dtype=torch.int32, device=dev); ex = torch.zeros(1, dtype=torch.uint8, device=dev)
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    grp = mg.KnotSplitGroup()
+    for _ in range(3):
+        lam.zero_(); grp.pcg(S, n, Sl, Pl, gl, lam, it, ex, cfg)
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        lam.zero_(); grp.pcg(S, n, Sl, Pl, gl, lam, it, ex, cfg)
+    e1.record(); torch.cuda.synchronize()
+    tt = torch.tensor([e0.elapsed_time(e1) / reps * 1e3], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    iters = int(it.item())
+    grp.close()
+    return {"knot_points": N, "knots_per_gpu": n, "solve_us": float(tt[0]), "iters": iters,
+            "us_per_iter": float(tt[0]) / max(iters, 1), "max_iter_exit": int(ex.item()),
+            "exchange": "tagged 8-byte NVLink peer stores into per-GPU mailboxes, polled locally; no NCCL in the solve"}
 
 
 def main():
@@ -276,6 +316,9 @@ def main():
     d2h = B * (4 * S * N + 4 + 1)
     hs.close()
 
+    ks = None
+    if world > 1 and not a.no_extras and 512 % world == 0 and 512 // world in (64, 128, 256):
+        ks = knotsplit_bench(torch, mg, dist, rank, world, dev, 512, a.tol)
     if rank == 0:
         peak, how = load_peaks()
         ms_per_step = total_ms / a.steps
@@ -306,6 +349,8 @@ def main():
                                               % (sample, r["schur_share"])}
             if not a.no_extras:
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
+        if ks is not None:
+            line["knot_split"] = ks
         print(json.dumps(line))
     if dist is not None:
         dist.destroy_process_group()
