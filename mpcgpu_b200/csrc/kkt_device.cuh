@@ -41,7 +41,8 @@ struct Cfg {
     static constexpr int PR = 44;               // floats per PROW row
     static constexpr int PK = S * PR + 8;       // floats per PROW knot (624 = 16 mod 32 banks)
     static constexpr int TK = S * S;            // floats per A / phi tile (196)
-    static constexpr int VK = 16;               // floats per vector slot
+    static constexpr int VK = 20;               // floats per vector slot (14 used; 80 B stride: the 4 or 8
+                                                // knots a warp reads land in distinct banks)
     static constexpr int cD = 0, cL = 14, cR = 28;   // column offsets of Pd | Pl | Pr in a row
     // shared-memory carve-up (float offsets)
     static constexpr int oP = 0;                        // [SLOTS][14][44]  PROW

@@ -86,7 +86,7 @@ size_t pcgSharedMemSize(uint32_t state_size, uint32_t knot_points) {
         const size_t slots = mpcb200_shim::KPC + 2;
         const size_t cl = mpcb200_shim::cluster_for(knot_points);
         // == Cfg<16, cl, 8>::SMEM_BYTES (kept in closed form because knot_points is a run-time value here)
-        bytes = sizeof(float) * (slots * (624 + 196 + 16 + 16) + 4 * 16 + 2 * ((cl * 4 + 3) & ~size_t(3)) + 4);
+        bytes = sizeof(float) * (slots * (624 + 196 + 20 + 20) + 4 * 20 + 2 * ((cl * 4 + 3) & ~size_t(3)) + 4);
     }
 #if MPCB200_SHIM_HAVE_DIMS
     // the reference launches with more than the 48 KB default and with cluster sizes up to 16:
