@@ -1,0 +1,236 @@
+// b200/sqp.cuh -- third linear-solver slot for MPCGPU ("LINSYS_SOLVE == 2"), next to
+// include/pcg/sqp.cuh (sqpSolvePcg) and include/qdldl/sqp.cuh (sqpSolveQdldl).
+//
+//   sqpSolveB200<T>(state_size, control_size, knot_points, timestep, d_eePos_traj, d_lambda,
+//                   d_xu, d_dynMem_const, pcg_config<T>&, T& rho, T rho_reset)
+//
+// Same arguments, same in/out buffers (d_lambda warm start, d_xu updated in place, rho adapted)
+// and the same 10-tuple as include/pcg/sqp.cuh:26,463-474, so include/mpcsim.cuh:249-277,303-307
+// can call it unchanged.  What differs from the PCG slot:
+//   * form_schur_system + cooperative pcg launch + two blocking read-backs
+//     (include/pcg/sqp.cuh:243-277) are ONE launch of mpcgpu_b200_kkt_solve_f32; S and Pinv are
+//     never materialised in HBM, the iteration count comes home asynchronously;
+//   * every buffer, stream and pinned mailbox lives in a workspace built on the first call and
+//     kept (the reference slot does ~20 cudaMalloc/cudaFree, 8 stream creates and a cuBLAS
+//     handle per SQP solve, inside its own 2 ms budget);
+//   * the accepted step xu += alpha dz is a 1-block kernel instead of a cuBLAS call.
+// The dynamics-facing kernels are the reference's own, included from where they are:
+// generate_kkt_submatrices (common/kkt.cuh), compute_dz (common/dz.cuh), compute_merit and
+// ls_gato_compute_merit (common/merit.cuh).  fp32 only (settings.cuh USE_DOUBLES 0).
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <tuple>
+#include <vector>
+#include <type_traits>
+#include <time.h>
+#include <cuda_runtime.h>
+#include "settings.cuh"
+#include "gpuassert.cuh"
+#include "types.cuh"
+#ifndef MPCGPU_B200_SLOT_COMMON_INCLUDED   // common/kkt.cuh and common/dz.cuh carry no include guard
+#include "common/kkt.cuh"
+#include "common/dz.cuh"
+#endif
+#include "merit.cuh"
+#include "mpcgpu_b200.h"
+
+namespace b200slot {
+
+constexpr uint32_t kAlphas = 8;       // step lengths 1, 1/2, ... 1/128 (include/pcg/sqp.cuh:63,410)
+constexpr float    kMu     = 10.0f;   // merit penalty (include/pcg/sqp.cuh:62,192)
+
+inline double us_between(const timespec& a, const timespec& b) {
+    return 1e6 * double(b.tv_sec - a.tv_sec) + 1e-3 * double(b.tv_nsec - a.tv_nsec);
+}
+
+template <typename T>
+__global__ void take_step(uint32_t n, T alpha, const T* __restrict__ dz, T* __restrict__ xu) {
+    for (uint32_t i = threadIdx.x + blockIdx.x * blockDim.x; i < n; i += blockDim.x * gridDim.x)
+        xu[i] += alpha * dz[i];
+}
+
+// What one (state_size, control_size, knot_points) needs on the device, carved out of a single
+// allocation; pinned host words for everything the host reads back.
+template <typename T>
+struct Workspace {
+    uint32_t s = 0, c = 0, N = 0;
+    char* d_pool = nullptr;
+    T *G = nullptr, *C = nullptr, *g = nullptr, *cv = nullptr, *dz = nullptr, *xs = nullptr;
+    T *merit0 = nullptr, *merits = nullptr, *merit_tmp = nullptr;
+    uint32_t* iters = nullptr;   // [SQP_MAX_ITER]
+    uint8_t*  flags = nullptr;   // [SQP_MAX_ITER]
+    struct Host { T merit0; T merits[kAlphas]; uint32_t iters[SQP_MAX_ITER]; uint8_t flags[SQP_MAX_ITER]; };
+    Host* h = nullptr;
+    cudaStream_t ls_stream[kAlphas] = {};
+    uint32_t nz = 0;             // length of xu / dz
+
+    static size_t up(size_t x) { return (x + 255) & ~size_t(255); }
+
+    void build(uint32_t s_, uint32_t c_, uint32_t N_) {
+        release();
+        s = s_; c = c_; N = N_;
+        nz = (s + c) * N - c;
+        const size_t nG = size_t(s * s + c * c) * N - c * c, nC = size_t(s * s + s * c) * (N - 1),
+                     ng = nz, nc = size_t(s) * N;
+        const size_t sz[] = {nG * sizeof(T), nC * sizeof(T), ng * sizeof(T), nc * sizeof(T), size_t(nz) * sizeof(T),
+                             s * sizeof(T), sizeof(T), kAlphas * sizeof(T), size_t(kAlphas) * N * sizeof(T),
+                             SQP_MAX_ITER * sizeof(uint32_t), SQP_MAX_ITER * sizeof(uint8_t)};
+        size_t off[12] = {0};
+        for (int i = 0; i < 11; i++) off[i + 1] = off[i] + up(sz[i]);
+        gpuErrchk(cudaMalloc(&d_pool, off[11]));
+        gpuErrchk(cudaMemset(d_pool, 0, off[11]));
+        G = (T*)(d_pool + off[0]);  C = (T*)(d_pool + off[1]);  g = (T*)(d_pool + off[2]);
+        cv = (T*)(d_pool + off[3]); dz = (T*)(d_pool + off[4]); xs = (T*)(d_pool + off[5]);
+        merit0 = (T*)(d_pool + off[6]); merits = (T*)(d_pool + off[7]); merit_tmp = (T*)(d_pool + off[8]);
+        iters = (uint32_t*)(d_pool + off[9]); flags = (uint8_t*)(d_pool + off[10]);
+        gpuErrchk(cudaMallocHost(&h, sizeof(Host)));
+        for (uint32_t i = 0; i < kAlphas; i++) gpuErrchk(cudaStreamCreate(&ls_stream[i]));
+    }
+    void release() {
+        if (!d_pool) return;
+        for (uint32_t i = 0; i < kAlphas; i++) cudaStreamDestroy(ls_stream[i]);
+        cudaFreeHost(h); cudaFree(d_pool);
+        d_pool = nullptr; h = nullptr;
+    }
+    ~Workspace() { /* process-lifetime object: the driver reclaims the memory at exit */ }
+};
+
+template <typename T>
+inline Workspace<T>& workspace(uint32_t s, uint32_t c, uint32_t N) {
+    static Workspace<T> w;
+    if (w.s != s || w.c != c || w.N != N || !w.d_pool) w.build(s, c, N);
+    return w;
+}
+
+}  // namespace b200slot
+
+template <typename T>
+auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const uint32_t knot_points, float timestep,
+                  T* d_eePos_traj, T* d_lambda, T* d_xu, void* d_dynMem_const, pcg_config<T>& config, T& rho,
+                  T rho_reset) {
+    static_assert(std::is_same<T, float>::value, "mpcgpu_b200 slot: fp32 only (settings.cuh USE_DOUBLES 0)");
+    using namespace b200slot;
+
+    std::vector<int> pcg_iter_vec;
+    std::vector<bool> pcg_exit_vec;
+    std::vector<double> linsys_time_vec, kkt_time_vec, schur_time_vec, dz_time_vec, line_search_time_vec;
+    bool sqp_time_exit = true;   // false only when rho runs away (include/pcg/sqp.cuh:395-399)
+    uint32_t sqp_iter = 0, solves = 0;
+
+    timespec t_begin, t_now, t_a, t_b;
+    gpuErrchk(cudaDeviceSynchronize());
+    clock_gettime(CLOCK_MONOTONIC, &t_begin);
+    auto out_of_time = [&]() -> bool {
+#if CONST_UPDATE_FREQ
+        clock_gettime(CLOCK_MONOTONIC, &t_now);
+        return us_between(t_begin, t_now) > SQP_MAX_TIME_US;
+#else
+        return false;
+#endif
+    };
+    // instrumentation brackets (blocking, like the reference's): compiled out unless asked for
+    auto lap_begin = [&](bool on) { if (on) { gpuErrchk(cudaDeviceSynchronize()); clock_gettime(CLOCK_MONOTONIC, &t_a); } };
+    auto lap_end = [&](bool on, std::vector<double>& v) {
+        if (on) { gpuErrchk(cudaDeviceSynchronize()); clock_gettime(CLOCK_MONOTONIC, &t_b); v.push_back(us_between(t_a, t_b)); }
+    };
+    constexpr bool fine = FINE_GRAINED_TIMING != 0, time_linsys = TIME_LINSYS != 0;
+
+    Workspace<T>& w = workspace<T>(state_size, control_size, knot_points);
+    gpuErrchk(cudaMemcpyAsync(w.xs, d_xu, state_size * sizeof(T), cudaMemcpyDeviceToDevice));
+    gpuErrchk(cudaMemsetAsync(w.merit0, 0, sizeof(T)));
+
+    const size_t merit_smem = get_merit_smem_size<T>(state_size, control_size);
+    const size_t ls_smem = get_merit_smem_size<T>(state_size, knot_points);   // as include/pcg/sqp.cuh:356
+    const size_t kkt_smem = 2 * get_kkt_smem_size<T>(state_size, control_size);
+    void* ls_kernel = (void*)ls_gato_compute_merit<T>;
+    uint32_t ks = state_size, kc = control_size, kn = knot_points;
+    T mu = kMu, dt = timestep;
+
+    compute_merit<T><<<knot_points, MERIT_THREADS, merit_smem>>>(state_size, control_size, knot_points, d_xu,
+                                                                  d_eePos_traj, mu, dt, d_dynMem_const, w.merit0);
+    gpuErrchk(cudaPeekAtLastError());
+    gpuErrchk(cudaMemcpyAsync(&w.h->merit0, w.merit0, sizeof(T), cudaMemcpyDeviceToHost));
+    bool merit0_home = false;
+    T merit_now = 0, drho = 1;
+    const T rho_factor = RHO_FACTOR, rho_max = RHO_MAX, rho_min = RHO_MIN;
+
+    for (uint32_t it = 0; it < SQP_MAX_ITER; it++) {
+        // 1. linearise: G, C, g, c
+        lap_begin(fine);
+        generate_kkt_submatrices<T><<<knot_points, KKT_THREADS, kkt_smem>>>(state_size, control_size, knot_points, w.G,
+                                                                            w.C, w.g, w.cv, d_dynMem_const, dt,
+                                                                            d_eePos_traj, w.xs, d_xu);
+        gpuErrchk(cudaPeekAtLastError());
+        lap_end(fine, kkt_time_vec);
+        if (out_of_time()) break;
+
+        // 2. Schur complement + preconditioner + PCG: one launch; lambda warm-started in place,
+        //    G becomes G^-1 in place for compute_dz
+        lap_begin(fine || time_linsys);
+        gpuErrchk((cudaError_t)mpcgpu_b200_kkt_solve_f32(state_size, control_size, knot_points, 1, w.G, w.C, w.g, w.cv,
+                                                         rho, d_lambda, config.pcg_max_iter, config.pcg_exit_tol,
+                                                         w.iters + solves, w.flags + solves, nullptr, nullptr));
+        gpuErrchk(cudaMemcpyAsync(&w.h->iters[solves], w.iters + solves, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+        gpuErrchk(cudaMemcpyAsync(&w.h->flags[solves], w.flags + solves, sizeof(uint8_t), cudaMemcpyDeviceToHost));
+        solves++;
+        lap_end(time_linsys, linsys_time_vec);
+        if (fine) schur_time_vec.push_back(0.0);   // Schur formation is inside the solve launch
+        if (out_of_time()) break;
+
+        // 3. dz from lambda
+        lap_begin(fine);
+        compute_dz(state_size, control_size, knot_points, w.G, w.C, w.g, d_lambda, w.dz);
+        gpuErrchk(cudaPeekAtLastError());
+        lap_end(fine, dz_time_vec);
+        if (out_of_time()) break;
+
+        // 4. parallel line search over 8 step lengths, one stream each
+        lap_begin(fine);
+        for (uint32_t p = 0; p < kAlphas; p++) {
+            void* args[] = {&ks, &kc, &kn, &w.xs, &d_xu, &d_eePos_traj, &mu, &dt, &d_dynMem_const, &w.dz, &p,
+                            &w.merits, &w.merit_tmp};
+            gpuErrchk(cudaLaunchCooperativeKernel(ls_kernel, knot_points, MERIT_THREADS, args, ls_smem, w.ls_stream[p]));
+        }
+        gpuErrchk(cudaPeekAtLastError());
+        lap_end(fine, line_search_time_vec);
+        if (out_of_time()) break;
+        // blocking copy on the legacy stream: waits for the 8 streams, the solve and its read-backs
+        gpuErrchk(cudaMemcpy(w.h->merits, w.merits, kAlphas * sizeof(T), cudaMemcpyDeviceToHost));
+        if (!merit0_home) { merit_now = w.h->merit0; merit0_home = true; }
+        if (out_of_time()) break;
+
+        uint32_t best = 0;
+        T best_merit = merit_now;
+        for (uint32_t i = 0; i < kAlphas; i++)
+            if (w.h->merits[i] < best_merit) { best_merit = w.h->merits[i]; best = i; }
+
+        if (best_merit == merit_now) {   // no step length improves: raise the regularisation
+            drho = max(drho * rho_factor, rho_factor);
+            rho = max(rho * drho, rho_min);
+            sqp_iter++;
+            if (rho > rho_max) { sqp_time_exit = false; rho = rho_reset; break; }
+            continue;
+        }
+        drho = min(drho / rho_factor, 1 / rho_factor);
+        rho = max(rho * drho, rho_min);
+        take_step<T><<<1, 256>>>(w.nz, T(-1.0) / T(1u << best), w.dz, d_xu);
+        gpuErrchk(cudaPeekAtLastError());
+        sqp_iter++;
+        if (out_of_time()) break;
+        merit_now = best_merit;
+    }
+
+    gpuErrchk(cudaPeekAtLastError());
+    gpuErrchk(cudaDeviceSynchronize());   // also lands every asynchronous read-back
+    timespec t_end;
+    clock_gettime(CLOCK_MONOTONIC, &t_end);
+    for (uint32_t i = 0; i < solves; i++) {
+        pcg_iter_vec.push_back(int(w.h->iters[i]));
+        pcg_exit_vec.push_back(w.h->flags[i] != 0);
+    }
+    const double sqp_solve_time = us_between(t_begin, t_end);
+    return std::make_tuple(pcg_iter_vec, linsys_time_vec, sqp_solve_time, sqp_iter, sqp_time_exit, pcg_exit_vec,
+                           kkt_time_vec, schur_time_vec, dz_time_vec, line_search_time_vec);
+}

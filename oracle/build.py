@@ -38,9 +38,10 @@ RUN = os.path.join(REFOUT, "run")            # working directory of the referenc
 HARNESS = os.path.join(RUN, "ref_harness")
 TRACK = os.path.join(RUN, "track_iiwa_pcg_n%d")
 TRACK_KNOTS = (32, 128)
+SLOT = os.path.join(RUN, "track_slot_%s_n%d")    # tools/track_slot.cu: simulateMPC over the pcg / b200 slot
 
 
-def _ref_nvcc(src, out, defs=()):
+def _ref_nvcc(src, out, defs=(), link_product=False):
     root = os.path.dirname(HERE)
     inc = [os.path.join(root, "mpcgpu_b200", "shim"), os.path.join(root, "include"),
            os.path.join(REF, "include"), os.path.join(REF, "include", "common"),
@@ -49,6 +50,8 @@ def _ref_nvcc(src, out, defs=()):
            os.path.join(HERE, "qdldl_cfg", "f32"), os.path.join(HERE, "qdldl_cfg")]
     cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-w", "-lineinfo"]
     cmd += list(defs) + [a for i in inc for a in ("-I", i)] + [src, "-o", out, "-lcublas"]
+    if link_product:   # the L2 slot calls the C ABI of mpcgpu_b200/libmpcgpu_b200.so
+        cmd += ["-L", os.path.join(root, "mpcgpu_b200"), "-lmpcgpu_b200", "-Xlinker", "-rpath=$ORIGIN/../../../mpcgpu_b200"]
     _run(cmd)
 
 
@@ -81,6 +84,18 @@ def _build_reference_cuda(force, verbose):
             _ref_nvcc(os.path.join(REF, "examples", "track_iiwa_pcg.cu"), out, ["-DKNOT_POINTS=%d" % n])
             if verbose:
                 print("built", out)
+    slot_src = os.path.join(root, "tools", "track_slot.cu")
+    slot_deps = deps + [slot_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "sqp.cuh")]
+    lib = os.path.join(root, "mpcgpu_b200", "libmpcgpu_b200.so")
+    for n in TRACK_KNOTS:
+        for name, flag in (("pcg", 0), ("b200", 1)):
+            out = SLOT % (name, n)
+            if flag and not os.path.exists(lib):
+                continue   # product library not built yet (mpcgpu_b200.build runs first in __graft_entry__.build)
+            if force or _stale(out, slot_deps):
+                _ref_nvcc(slot_src, out, ["-DKNOT_POINTS=%d" % n, "-DSLOT_B200=%d" % flag], link_product=bool(flag))
+                if verbose:
+                    print("built", out)
 
 
 def build(force=False, verbose=False):

@@ -106,3 +106,22 @@ def test_shim_pcg_launched_like_the_reference_slot(N, tol, tmp_path):
     assert abs(it_g - it_o) <= 1 and ex_g == ex_o, (it_g, it_o)
     lam_s, _, _ = oracle.pcg(S, N, S32, P32, g32, lam0, it_g, 0.0)
     assert rel(lam_g, lam_s) < max(1e-4, 3.0 * oracle.pcg_noise_floor(S, N, S32, P32, g32, lam0, it_g))
+
+
+def test_closed_loop_tracking_through_the_b200_slot():
+    """The reference's unchanged simulateMPC (include/mpcsim.cuh) with its solver call bound to
+    mpcgpu_b200/shim/b200/sqp.cuh (tools/track_slot.cu): the IIWA arm must keep tracking the 0_0
+    figure-eight, every control step must get at least the SQP iterations the PCG slot gets."""
+    import json
+    exe = os.path.join(RUN, "track_slot_b200_n32")
+    if not os.path.exists(exe):
+        pytest.fail("oracle/_ref/run/track_slot_b200_n32 missing: run oracle/build.py where /root/reference exists")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+    r = subprocess.run([exe, "5e-6"], cwd=RUN, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.stdout[-400:], r.stderr[-400:])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["control_steps"] > 1000
+    assert out["sqp_iters_mean"] >= 3.0            # PCG slot on the same box: 3.8 (profiles/r1_track_slot.jsonl)
+    assert np.isfinite(out["tracking_err_mean"]) and out["tracking_err_mean"] < 0.25   # PCG slot: 0.10
+    assert out["final_tracking_err"] < 0.25
