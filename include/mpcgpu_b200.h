@@ -81,6 +81,22 @@ int mpcgpu_b200_kkt_solve_f32(uint32_t state_size, uint32_t control_size, uint32
                               float exit_tol, uint32_t* d_iters, uint8_t* d_max_iter_exit,
                               void* d_ws, void* stream);
 
+/* The same launch with the primal-step recovery as epilogue: compute_dz,
+ * include/common/dz.cuh:124-133 (kernel :3-121), called at include/pcg/sqp.cuh:300-309.
+ * d_dz: [(s+c)*N - c] per instance, the layout of d_xu.  Replaces one more launch and one more
+ * pass over G^-1, C, g of the reference's SQP iteration. */
+int mpcgpu_b200_kkt_solve_dz_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                                 uint32_t batch, float* d_G, const float* d_C, const float* d_g,
+                                 const float* d_c, float rho, float* d_lambda, float* d_dz,
+                                 uint32_t max_iter, float exit_tol, uint32_t* d_iters,
+                                 uint8_t* d_max_iter_exit, void* d_ws, void* stream);
+
+/* compute_dz alone (include/common/dz.cuh:124-133): d_Ginv = d_G after mpcgpu_b200_schur_f32 /
+ * kkt_solve, d_C, d_g as given to them, d_lambda the multipliers.  Batched like the rest. */
+int mpcgpu_b200_dz_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                       uint32_t batch, const float* d_Ginv, const float* d_C, const float* d_g,
+                       const float* d_lambda, float* d_dz, void* stream);
+
 /* Reference-STYLE PCG (one CTA per knot, 4 grid barriers per iteration, cooperative launch):
  * our restatement of the reference kernel's structure, kept as the in-repo
  * comparison kernel and as the kernel behind the header shim's pcg<T,S,N>.  batch == 1.

@@ -8,8 +8,8 @@ include/pcg/sqp.cuh), synth.py (seeded synthetic KKT blocks).
 """
 from . import synth  # noqa: F401
 from .api import (HostSolver, KnotSplitGroup, MpcGpuError, PcgConfig, epoch_stride,  # noqa: F401
-                  form_schur_system, kkt_solve, knot_range, knotsplit_pcg, launch_count, lib,
+                  compute_dz, form_schur_system, kkt_solve, kkt_solve_dz, knot_range, knotsplit_pcg, launch_count, lib,
                   mailbox_bytes, pcg, schur_slice, sizes)
 
-__all__ = ["HostSolver", "MpcGpuError", "PcgConfig", "form_schur_system", "kkt_solve", "pcg",
+__all__ = ["HostSolver", "MpcGpuError", "PcgConfig", "form_schur_system", "kkt_solve", "kkt_solve_dz", "compute_dz", "pcg",
            "sizes", "synth", "lib", "launch_count"]

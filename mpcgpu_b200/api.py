@@ -150,6 +150,39 @@ def kkt_solve(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, 
     _check(rc, "kkt_solve")
 
 
+def kkt_solve_dz(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, d_c, rho,
+                 d_lambda, d_dz, d_pcg_iters, d_pcg_exit, config: PcgConfig, batch=1):
+    """kkt_solve with compute_dz (include/common/dz.cuh:124-133) as the kernel's epilogue."""
+    s, c, N = state_size, control_size, knot_points
+    z = sizes(s, c, N)
+    f = torch.float32
+    rc = lib().mpcgpu_b200_kkt_solve_dz_f32(
+        ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
+        _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
+        _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
+        _ptr(d_g, f, "d_g", z["g"] * batch), _ptr(d_c, f, "d_c", z["c"] * batch),
+        ctypes.c_float(rho), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
+        _ptr(d_dz, f, "d_dz", z["g"] * batch),
+        ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+        _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", batch),
+        _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", batch), None, _stream())
+    _check(rc, "kkt_solve_dz")
+
+
+def compute_dz(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g_val, d_lambda, d_dz, batch=1):
+    """compute_dz of include/common/dz.cuh:124-133 (same argument order): d_G_dense holds G^-1."""
+    s, c, N = state_size, control_size, knot_points
+    z = sizes(s, c, N)
+    f = torch.float32
+    rc = lib().mpcgpu_b200_dz_f32(
+        ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
+        _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
+        _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
+        _ptr(d_g_val, f, "d_g_val", z["g"] * batch), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
+        _ptr(d_dz, f, "d_dz", z["g"] * batch), _stream())
+    _check(rc, "compute_dz")
+
+
 def launch_count():
     return int(lib().mpcgpu_b200_launch_count())
 

@@ -2,6 +2,7 @@
 // No torch, no CPU fallback: every compute entry point launches sm_100a kernels or fails.
 #include "../../include/mpcgpu_b200.h"
 
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -189,6 +190,38 @@ int mpcgpu_b200_kkt_solve_f32(uint32_t s, uint32_t c, uint32_t N, uint32_t batch
     a.iters = d_iters; a.exits = d_max_iter_exit;
     cudaError_t e = dispatch<K_FUSED>(a, (cudaStream_t)stream);
     return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_kkt_solve_f32");
+}
+
+int mpcgpu_b200_kkt_solve_dz_f32(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, float* d_G,
+                                 const float* d_C, const float* d_g, const float* d_c, float rho,
+                                 float* d_lambda, float* d_dz, uint32_t max_iter, float exit_tol,
+                                 uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws, void* stream) {
+    (void)d_ws;
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_kkt_solve_dz_f32: unsupported sizes (need s=14,c=7,1<=N<=512)");
+    if (!d_G || (N > 1 && !d_C) || !d_g || !d_c || !d_lambda || !d_dz || !d_iters || !d_max_iter_exit) return bad("mpcgpu_b200_kkt_solve_dz_f32: null pointer");
+    BatchArgs a = make_args(s, c, N, batch);
+    a.G = d_G; a.C = d_C; a.g = d_g; a.c = d_c; a.rho = rho;
+    a.lambda = d_lambda; a.max_iter = max_iter; a.exit_tol = exit_tol;
+    a.iters = d_iters; a.exits = d_max_iter_exit;
+    a.dz = d_dz; a.sdz = a.sg;
+    cudaError_t e = dispatch<K_FUSED>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_kkt_solve_dz_f32");
+}
+
+int mpcgpu_b200_dz_f32(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, const float* d_Ginv,
+                       const float* d_C, const float* d_g, const float* d_lambda, float* d_dz, void* stream) {
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_dz_f32: unsupported sizes (need s=14,c=7,1<=N<=512)");
+    if (!d_Ginv || (N > 1 && !d_C) || !d_g || !d_lambda || !d_dz) return bad("mpcgpu_b200_dz_f32: null pointer");
+    BatchArgs a = make_args(s, c, N, batch);
+    a.G = const_cast<float*>(d_Ginv); a.C = d_C; a.g = d_g; a.lambda = const_cast<float*>(d_lambda);
+    a.dz = d_dz; a.sdz = a.sg;
+    const size_t knots = (size_t)batch * N;
+    const unsigned grid = (unsigned)std::min<size_t>((knots + 31) / 32, 148u * 64u);
+    dz_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(e, "mpcgpu_b200_dz_f32");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return 0;
 }
 
 int mpcgpu_b200_pcg_refstyle_f32(uint32_t s, uint32_t N, const float* d_S, const float* d_Pinv,

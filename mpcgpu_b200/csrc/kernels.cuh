@@ -5,6 +5,7 @@
 // (the reference's single-instance buffers, concatenated).
 #pragma once
 #include "kkt_device.cuh"
+#include "dz_device.cuh"
 
 namespace mpcb200 {
 
@@ -19,6 +20,7 @@ struct BatchArgs {
     float* lambda;
     unsigned max_iter; float exit_tol;
     unsigned* iters; uint8_t* exits;
+    float* dz = nullptr; size_t sdz = 0;   // optional compute_dz epilogue (fused) / output of dz_kernel
 };
 
 // PROW column offset of block column `blk` (0 left, 1 diag, 2 right) of the reference layout
@@ -136,8 +138,6 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_kernel(BatchArgs a) 
                  a.exits + b);
 }
 
-// fused KKT solve: S and Pinv never leave the SM (Def. B traffic: read G,C,g,c,lambda0;
-// write lambda, G^-1).
 template <class CF>
 __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a) {
     extern __shared__ float4 smem4[];
@@ -148,6 +148,22 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a
     schur_rows<CF>(smem, P, a.N, a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
+    if (a.dz) {   // compute_dz epilogue: lambda and G^-1 were written by this cluster, read back through L2
+        if (CF::CL == 1) __syncthreads();   // CL > 1: pcg_rows ended on a cluster barrier (release/acquire)
+        dz_rows(P.G, P.C, P.g, a.lambda + b * a.sv, a.dz + b * a.sdz, a.N, (int)cluster_rank<CF::CL>() * CF::KPC, CF::KPC);
+    }
+}
+
+// compute_dz alone (include/common/dz.cuh:124-133): 32 knots per 256-thread CTA over the whole batch
+__global__ void __launch_bounds__(256) dz_kernel(BatchArgs a) {
+    const int t = threadIdx.x & 7, lane = threadIdx.x & 31, base = lane & ~7;
+    const unsigned mask = 0xFFu << base;
+    const size_t total = (size_t)a.batch * a.N;
+    for (size_t gk = (size_t)blockIdx.x * 32 + (threadIdx.x >> 3); gk < total; gk += (size_t)gridDim.x * 32) {
+        const size_t b = gk / a.N;
+        const int k = (int)(gk - b * a.N);
+        dz_knot(a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.lambda + b * a.sv, a.dz + b * a.sdz, a.N, k, t, mask, base);
+    }
 }
 
 // ---- knot-range split across GPUs (BASELINE.json configs[3]) -----------------------------------

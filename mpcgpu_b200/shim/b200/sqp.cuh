@@ -7,16 +7,16 @@
 // Same arguments, same in/out buffers (d_lambda warm start, d_xu updated in place, rho adapted)
 // and the same 10-tuple as include/pcg/sqp.cuh:26,463-474, so include/mpcsim.cuh:249-277,303-307
 // can call it unchanged.  What differs from the PCG slot:
-//   * form_schur_system + cooperative pcg launch + two blocking read-backs
-//     (include/pcg/sqp.cuh:243-277) are ONE launch of mpcgpu_b200_kkt_solve_f32; S and Pinv are
+//   * form_schur_system + cooperative pcg launch + two blocking read-backs + compute_dz
+//     (include/pcg/sqp.cuh:243-309) are ONE launch of mpcgpu_b200_kkt_solve_dz_f32; S and Pinv are
 //     never materialised in HBM, the iteration count comes home asynchronously;
 //   * every buffer, stream and pinned mailbox lives in a workspace built on the first call and
 //     kept (the reference slot does ~20 cudaMalloc/cudaFree, 8 stream creates and a cuBLAS
 //     handle per SQP solve, inside its own 2 ms budget);
 //   * the accepted step xu += alpha dz is a 1-block kernel instead of a cuBLAS call.
 // The dynamics-facing kernels are the reference's own, included from where they are:
-// generate_kkt_submatrices (common/kkt.cuh), compute_dz (common/dz.cuh), compute_merit and
-// ls_gato_compute_merit (common/merit.cuh).  fp32 only (settings.cuh USE_DOUBLES 0).
+// generate_kkt_submatrices (common/kkt.cuh), compute_merit and ls_gato_compute_merit
+// (common/merit.cuh).  fp32 only (settings.cuh USE_DOUBLES 0).
 #pragma once
 #include <cstdint>
 #include <cstdio>
@@ -166,24 +166,18 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
         lap_end(fine, kkt_time_vec);
         if (out_of_time()) break;
 
-        // 2. Schur complement + preconditioner + PCG: one launch; lambda warm-started in place,
-        //    G becomes G^-1 in place for compute_dz
+        // 2.+3. Schur complement + preconditioner + PCG + dz recovery: one launch; lambda warm-started
+        //    in place, G becomes G^-1 in place, dz = compute_dz(G^-1, C, g, lambda) as the kernel's epilogue
         lap_begin(fine || time_linsys);
-        gpuErrchk((cudaError_t)mpcgpu_b200_kkt_solve_f32(state_size, control_size, knot_points, 1, w.G, w.C, w.g, w.cv,
-                                                         rho, d_lambda, config.pcg_max_iter, config.pcg_exit_tol,
-                                                         w.iters + solves, w.flags + solves, nullptr, nullptr));
+        gpuErrchk((cudaError_t)mpcgpu_b200_kkt_solve_dz_f32(state_size, control_size, knot_points, 1, w.G, w.C, w.g,
+                                                            w.cv, rho, d_lambda, w.dz, config.pcg_max_iter,
+                                                            config.pcg_exit_tol, w.iters + solves, w.flags + solves,
+                                                            nullptr, nullptr));
         gpuErrchk(cudaMemcpyAsync(&w.h->iters[solves], w.iters + solves, sizeof(uint32_t), cudaMemcpyDeviceToHost));
         gpuErrchk(cudaMemcpyAsync(&w.h->flags[solves], w.flags + solves, sizeof(uint8_t), cudaMemcpyDeviceToHost));
         solves++;
         lap_end(time_linsys, linsys_time_vec);
-        if (fine) schur_time_vec.push_back(0.0);   // Schur formation is inside the solve launch
-        if (out_of_time()) break;
-
-        // 3. dz from lambda
-        lap_begin(fine);
-        compute_dz(state_size, control_size, knot_points, w.G, w.C, w.g, d_lambda, w.dz);
-        gpuErrchk(cudaPeekAtLastError());
-        lap_end(fine, dz_time_vec);
+        if (fine) { schur_time_vec.push_back(0.0); dz_time_vec.push_back(0.0); }   // both inside the solve launch
         if (out_of_time()) break;
 
         // 4. parallel line search over 8 step lengths, one stream each

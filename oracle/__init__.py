@@ -27,7 +27,7 @@ _libs = {}
 
 def _lib(name):
     if not _libs:
-        paths = _build.build()
+        paths = _build.build(reference_cuda=False)
         for k, p in paths.items():
             _libs[k] = ctypes.CDLL(p)
     return _libs[name]

@@ -74,31 +74,34 @@ def _build_reference_cuda(force, verbose):
         dst = os.path.join(RUN, "examples", "trajfiles", f)
         if not os.path.exists(dst):
             shutil.copyfile(os.path.join(REF, "examples", "trajfiles", f), dst)
+    jobs = []   # (src, out, defs, link_product)
     if force or _stale(HARNESS, deps):
-        _ref_nvcc(os.path.join(HERE, "ref_harness.cu"), HARNESS)
-        if verbose:
-            print("built", HARNESS)
+        jobs.append((os.path.join(HERE, "ref_harness.cu"), HARNESS, [], False))
     for n in TRACK_KNOTS:
-        out = TRACK % n
-        if force or _stale(out, deps):
-            _ref_nvcc(os.path.join(REF, "examples", "track_iiwa_pcg.cu"), out, ["-DKNOT_POINTS=%d" % n])
-            if verbose:
-                print("built", out)
+        if force or _stale(TRACK % n, deps):
+            jobs.append((os.path.join(REF, "examples", "track_iiwa_pcg.cu"), TRACK % n, ["-DKNOT_POINTS=%d" % n], False))
     slot_src = os.path.join(root, "tools", "track_slot.cu")
-    slot_deps = deps + [slot_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "sqp.cuh")]
+    slot_deps = deps + [slot_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "sqp.cuh"),
+                        os.path.join(root, "include", "mpcgpu_b200.h")]
     lib = os.path.join(root, "mpcgpu_b200", "libmpcgpu_b200.so")
     for n in TRACK_KNOTS:
         for name, flag in (("pcg", 0), ("b200", 1)):
-            out = SLOT % (name, n)
             if flag and not os.path.exists(lib):
                 continue   # product library not built yet (mpcgpu_b200.build runs first in __graft_entry__.build)
-            if force or _stale(out, slot_deps):
-                _ref_nvcc(slot_src, out, ["-DKNOT_POINTS=%d" % n, "-DSLOT_B200=%d" % flag], link_product=bool(flag))
-                if verbose:
-                    print("built", out)
+            if force or _stale(SLOT % (name, n), slot_deps):
+                jobs.append((slot_src, SLOT % (name, n), ["-DKNOT_POINTS=%d" % n, "-DSLOT_B200=%d" % flag], bool(flag)))
+    if jobs:   # each is a minute of nvcc on the GRiD dynamics headers: run them side by side
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(len(jobs), max(1, (os.cpu_count() or 2) // 2))) as ex:
+            for _ in ex.map(lambda j: _ref_nvcc(j[0], j[1], j[2], link_product=j[3]), jobs):
+                pass
+        if verbose:
+            print("built", *[j[1] for j in jobs])
 
 
-def build(force=False, verbose=False):
+def build(force=False, verbose=False, reference_cuda=True):
+    """reference_cuda=False (what `import oracle` uses) builds only the C libraries -- seconds; the
+    reference's CUDA executables (minutes of nvcc) are built by __graft_entry__.build() / `python -m oracle.build`."""
     os.makedirs(BUILD, exist_ok=True)
     os.makedirs(REFOUT, exist_ok=True)
     own = [os.path.join(HERE, f) for f in ("mpc_oracle.c", "oracle_impl.h")]
@@ -129,7 +132,8 @@ def build(force=False, verbose=False):
                   *i32, "-o", base, "cpu_baseline.c", "mpc_oracle.c", qsrc, "-lm"])
         if verbose:
             print("built", f32, f64, base)
-        _build_reference_cuda(force, verbose)
+        if reference_cuda:
+            _build_reference_cuda(force, verbose)
     else:
         missing = [p for p in (f32, f64, base) if not os.path.exists(p)]
         if missing:

@@ -260,3 +260,29 @@ def test_errors_are_loud():
     with pytest.raises(mg.MpcGpuError):
         t = torch.zeros(10)
         mg.form_schur_system(S, C, 4, t, t, t, t, t, t, t, 1e-3)        # CPU tensors: no fallback
+
+
+@pytest.mark.parametrize("N", [1, 2, 5, 32, 64, 96, 128, 512])
+def test_compute_dz_matches_oracle_standalone_and_as_epilogue(N):
+    """compute_dz (include/common/dz.cuh:3-133): standalone kernel against the oracle on identical
+    (G^-1, C, g, lambda); the fused kernel's epilogue must give the standalone kernel's bits."""
+    B = 3
+    d = synth.gen_kkt(N, B, seed=synth.BASE_SEED + 11 * N)
+    cfg = mg.PcgConfig(pcg_exit_tol=1e-5)
+    G, Cm, g, cv = dev(d["G"]), dev(d["C"]), dev(d["g"]), dev(d["c"])
+    lam = torch.zeros((B, S * N), device=DEV)
+    it = torch.zeros(B, dtype=torch.int32, device=DEV)
+    ex = torch.zeros(B, dtype=torch.uint8, device=DEV)
+    nz = (S + C) * N - C
+    dz_f = torch.full((B, nz), float("nan"), device=DEV)
+    mg.kkt_solve_dz(S, C, N, G, Cm, g, cv, d["rho"], lam, dz_f, it, ex, cfg, batch=B)
+    dz_s = torch.full((B, nz), float("nan"), device=DEV)
+    mg.compute_dz(S, C, N, G, Cm, g, lam, dz_s, batch=B)   # G now holds G^-1
+    torch.cuda.synchronize()
+    assert torch.equal(dz_f, dz_s)
+    Gi, lam_h, dz_h = G.cpu().numpy(), lam.cpu().numpy(), dz_s.cpu().numpy()
+    assert np.all(np.isfinite(dz_h))
+    for b in range(B):
+        ref32 = oracle.dz(S, C, N, Gi[b], d["C"][b], d["g"][b], lam_h[b], np.float32)
+        ref64 = oracle.dz(S, C, N, Gi[b], d["C"][b], d["g"][b], lam_h[b], np.float64)
+        assert rel(dz_h[b], ref64) < max(1e-4, 4.0 * rel(ref32, ref64))
