@@ -33,7 +33,7 @@ def lib():
     """Load (once) the in-tree CUDA library; raises loudly if it is absent."""
     global _LIB
     if _LIB is None:
-        path = _build.LIB
+        path = os.environ.get("MPCGPU_B200_LIB", _build.LIB)   # an alternative BUILD of this library (A/B experiments)
         if not os.path.exists(path):
             raise MpcGpuError(
                 "%s not found: build it with `python -m mpcgpu_b200.build` "

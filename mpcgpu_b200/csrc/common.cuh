@@ -74,6 +74,74 @@ __device__ __forceinline__ void st_async_f32(uint32_t cluster_addr, float v, uin
                  "r"(__float_as_uint(v)), "r"(cluster_mbar) : "memory");
 }
 
+// ---- tensor memory (TMEM, 128 lanes x 512 columns x 32 bit per SM) as an operand store ----------
+// tcgen05.ld/st .32x32b: warp w of the CTA addresses lanes 32*(w%4)..+31, thread = lane, xN = N
+// consecutive 32-bit columns of that lane.  Measured on B200 (tools/tmem_bw.cu): >= 300 B/clk/SM,
+// concurrent with (not taken from) the 128 B/clk shared-memory pipe.
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_word, uint32_t ncols) {   // whole warp; ncols pow2 >= 32
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_word)), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {      // whole warp
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+template <int N> struct TmemChunk;   // N floats of one lane: asynchronous load, wait, store
+template <> struct TmemChunk<16> {
+    uint32_t q[16];
+    __device__ __forceinline__ void ld(uint32_t a) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                     : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7]),
+                       "=r"(q[8]), "=r"(q[9]), "=r"(q[10]), "=r"(q[11]), "=r"(q[12]), "=r"(q[13]), "=r"(q[14]), "=r"(q[15])
+                     : "r"(a) : "memory");
+    }
+    // the registers pass THROUGH the wait so no use of them can be scheduled above it
+    __device__ __forceinline__ void wait() {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(q[0]), "+r"(q[1]), "+r"(q[2]), "+r"(q[3]), "+r"(q[4]), "+r"(q[5]), "+r"(q[6]), "+r"(q[7]),
+                       "+r"(q[8]), "+r"(q[9]), "+r"(q[10]), "+r"(q[11]), "+r"(q[12]), "+r"(q[13]), "+r"(q[14]), "+r"(q[15])
+                     :: "memory");
+    }
+    __device__ __forceinline__ void st(uint32_t a) const {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+                     ::"r"(a), "r"(q[0]), "r"(q[1]), "r"(q[2]), "r"(q[3]), "r"(q[4]), "r"(q[5]), "r"(q[6]), "r"(q[7]),
+                       "r"(q[8]), "r"(q[9]), "r"(q[10]), "r"(q[11]), "r"(q[12]), "r"(q[13]), "r"(q[14]), "r"(q[15]) : "memory");
+    }
+};
+template <> struct TmemChunk<8> {
+    uint32_t q[8];
+    __device__ __forceinline__ void ld(uint32_t a) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7])
+                     : "r"(a) : "memory");
+    }
+    __device__ __forceinline__ void wait() {
+        asm volatile("tcgen05.wait::ld.sync.aligned;"
+                     : "+r"(q[0]), "+r"(q[1]), "+r"(q[2]), "+r"(q[3]), "+r"(q[4]), "+r"(q[5]), "+r"(q[6]), "+r"(q[7]) :: "memory");
+    }
+    __device__ __forceinline__ void st(uint32_t a) const {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                     ::"r"(a), "r"(q[0]), "r"(q[1]), "r"(q[2]), "r"(q[3]), "r"(q[4]), "r"(q[5]), "r"(q[6]), "r"(q[7]) : "memory");
+    }
+};
+template <> struct TmemChunk<4> {
+    uint32_t q[4];
+    __device__ __forceinline__ void ld(uint32_t a) {
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]) : "r"(a) : "memory");
+    }
+    __device__ __forceinline__ void wait() {
+        asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(q[0]), "+r"(q[1]), "+r"(q[2]), "+r"(q[3]) :: "memory");
+    }
+    __device__ __forceinline__ void st(uint32_t a) const {
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1,%2,%3,%4};"
+                     ::"r"(a), "r"(q[0]), "r"(q[1]), "r"(q[2]), "r"(q[3]) : "memory");
+    }
+};
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -28,8 +28,18 @@
 
 namespace mpcb200 {
 
-template <int KPC_, int CL_, int LPK_>
+#ifndef MPCB200_TM_WPC
+#define MPCB200_TM_WPC 1
+#endif
+#ifndef MPCB200_PINV_TMEM
+#define MPCB200_PINV_TMEM 1   // 0: Pinv rows stay in shared memory during the PCG phase (A/B builds)
+#endif
+constexpr int pow2_at_least(int x) { int p = 32; while (p < x) p *= 2; return p; }
+
+// TM_ = 1: the PCG phase keeps the Pinv rows in tensor memory instead of shared memory
+template <int KPC_, int CL_, int LPK_, int TM_ = MPCB200_PINV_TMEM>
 struct Cfg {
+    static constexpr bool TM = TM_ != 0;
     static constexpr int S = 14, C = 7;
     static constexpr int KPC = KPC_, CL = CL_;
     static constexpr int LPK = LPK_;            // lanes per knot
@@ -54,9 +64,17 @@ struct Cfg {
     static constexpr int NREDP = (NRED + 3) & ~3;
     static constexpr int oRed = oHal + 4 * VK;          // [2 bufs][NREDP]
     static constexpr int oMb = oRed + 2 * NREDP;        // 2 mbarriers (8 B each), cluster kernels
-    static constexpr int FLOATS = oMb + 4;
+    static constexpr int oTm = oMb + 4;                 // TMEM base address of this CTA (+ pad)
+    static constexpr int FLOATS = oTm + 4;
+    // tensor-memory copy of Pinv: per lane 3 parts x 7 column pairs x RPT rows, in chunks of 2*RPT floats
+    static constexpr int TWPC = MPCB200_TM_WPC;         // column pairs per chunk
+    static constexpr int TCH = 2 * RPT * TWPC;          // floats per tcgen05.ld (x4 / x8 / x16)
+    static constexpr int TNCH = (21 + TWPC - 1) / TWPC; // chunks per matvec
+    static constexpr int TPT = TNCH * TCH;              // columns per thread
+    static constexpr int TCOLS = pow2_at_least(((NW + 3) / 4) * TPT);   // allocation, power of two <= 512
+    static_assert(!TM || TCOLS <= 512, "tensor memory has 512 columns");
     static constexpr size_t SMEM_BYTES = sizeof(float) * FLOATS;
-    static constexpr int MIN_CTAS = (LPK == 4) ? 1 : (512 / NT > 0 ? 512 / NT : 1);
+    static constexpr int MIN_CTAS = (LPK == 4) ? (256 / NT > 0 ? 256 / NT : 1) : (512 / NT > 0 ? 512 / NT : 1);
     static_assert(LPK == 4 || LPK == 8, "4 or 8 lanes per knot");
     static_assert(NT % 32 == 0 && NT <= 1024, "whole warps, <= 1024 threads");
     static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory of sm_100");
@@ -669,6 +687,14 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     const unsigned hb = (CL > 1) ? ((has_l ? 56u : 0u) + (has_r ? 56u : 0u)) : 0u;   // halo bytes per phase
     if (CL > 1 && tid == 0) { mbar_init(mb, 1); mbar_init(mb + 1, 1); fence_mbar_init_cluster(); }
     const float* myP = smem + CF::oP + sl * PK;
+    constexpr bool TM = CF::TM;
+    constexpr int TCH = CF::TCH;
+    uint32_t* tm_word = reinterpret_cast<uint32_t*>(smem + CF::oTm);
+    uint32_t tcol = 0;      // TMEM address of this lane's first column
+    if (TM) {               // published by the barriers below, long before the first use
+        if (tid < 32) tmem_alloc(tm_word, CF::TCOLS);
+        tmem_fence_before_sync();
+    }
 
     // y(rows) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
     auto s_mv = [&](const float* vec, float (&y)[RPT]) {
@@ -706,6 +732,41 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             y[j] = rm.ok[j] ? (hsum(acc[1]) + hsum(acc[0])) + hsum(acc[2]) : 0.f;
         }
     };
+    // same rows from tensor memory: chunk (part, w) = column pair w of all my RPT rows of block `part`
+    // (0 Pd, 1 Pl, 2 Pr); the accumulation order per row is the one of p_mv -> identical bits.
+    // Loads run one chunk ahead of the FFMA2s; shared memory only delivers the three x vectors.
+    auto p_mv_tm = [&](const float* vec, float (&y)[RPT]) {
+        constexpr int WPC = CF::TWPC, NCH = CF::TNCH;
+        TmemChunk<TCH> buf[2];
+        float part_sum[RPT];
+        buf[0].ld(tcol);
+#pragma unroll
+        for (int part = 0; part < 3; part++) {
+            float2 x[7];
+            ld14_v4(x, vec + (sl + (part == 0 ? 0 : (part == 1 ? -1 : 1))) * VK);
+            float2 acc[RPT];
+#pragma unroll
+            for (int j = 0; j < RPT; j++) acc[j] = splat(0.f);
+#pragma unroll
+            for (int w = 0; w < 7; w++) {
+                const int pi = part * 7 + w, c = pi / WPC, o = (pi % WPC) * 2 * RPT;
+                if (pi % WPC == 0) {     // tcgen05.wait::ld covers every load in flight: wait, THEN start the next
+                    buf[c & 1].wait();
+                    if (c + 1 < NCH) buf[(c + 1) & 1].ld(tcol + (c + 1) * TCH);
+                }
+#pragma unroll
+                for (int j = 0; j < RPT; j++)
+                    acc[j] = fma2(f2(__uint_as_float(buf[c & 1].q[o + 2 * j]), __uint_as_float(buf[c & 1].q[o + 2 * j + 1])), x[w], acc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                if (part == 0) part_sum[j] = hsum(acc[j]);
+                else if (part == 1) part_sum[j] = hsum(acc[j]) + part_sum[j];
+                else y[j] = rm.ok[j] ? part_sum[j] + hsum(acc[j]) : 0.f;
+            }
+        }
+    };
+    auto pinv_mv = [&](const float* vec, float (&y)[RPT]) { if constexpr (TM) p_mv_tm(vec, y); else p_mv(vec, y); };
     auto put = [&](float* dst, const float (&v)[RPT]) {        // my rows of a 16-float vector slot
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) dst[rm.row[j]] = v[j];
@@ -788,8 +849,30 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     if (SPLIT) gpull_rows(3, tg0, hl_r, hr_r);
     cluster_sync_all<CL>();
 
+    if (TM) {   // PROW is final (barrier above): move my Pinv rows into tensor memory
+        tmem_fence_after_sync();
+        const int warp = tid >> 5;
+        tcol = *tm_word + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * CF::TPT);
+#pragma unroll
+        for (int c = 0; c < CF::TNCH; c++) {
+            TmemChunk<TCH> ch;
+#pragma unroll
+            for (int u = 0; u < CF::TWPC; u++) {
+                const int pi = c * CF::TWPC + u, part = pi / 7, w = pi % 7;
+                const int colofs = (part == 0 ? CF::cD : (part == 1 ? CF::cL : CF::cR)) + 2 * w;
+#pragma unroll
+                for (int j = 0; j < RPT; j++) {
+                    float2 v = f2(0.f, 0.f);
+                    if (pi < 21) v = *reinterpret_cast<const float2*>(myP + rm.row[j] * PR + colofs);
+                    ch.q[u * 2 * RPT + 2 * j] = __float_as_uint(v.x); ch.q[u * 2 * RPT + 2 * j + 1] = __float_as_uint(v.y);
+                }
+            }
+            ch.st(tcol + c * TCH);
+        }
+        tmem_wait_st();
+    }
     // ---- p = rt = Pinv r ; eta = r.rt ----------------------------------------------------------
-    p_mv(rv, rt);
+    pinv_mv(rv, rt);
 #pragma unroll
     for (int j = 0; j < RPT; j++) pp[j] = rt[j];
     put(pv + sl * VK, pp);                   // pv was last read before the barrier above
@@ -839,7 +922,7 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
         }
         __syncthreads();
         // ---- rt = Pinv r ; eta_new = r.rt ----------------------------------------------------
-        p_mv(rv, rt);
+        pinv_mv(rv, rt);
         if (CL > 1) {
             if (first_g && has_l) push(hal + (1 * 2 + 1) * VK, rank - 1, 1, rt);
             if (last_g && has_r)  push(hal + (1 * 2 + 0) * VK, rank + 1, 1, rt);
@@ -881,6 +964,11 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     if (rank == 0 && tid == 0) { *d_iters = iter; *d_exit = max_iter_exit ? 1 : 0; }
     // no CTA may exit while a peer can still address its shared memory
     if (CL > 1) cluster_sync_all<CL>();
+    if (TM) {
+        tmem_fence_before_sync();
+        __syncthreads();
+        if (tid < 32) tmem_dealloc(*tm_word, CF::TCOLS);
+    }
 }
 
 }  // namespace mpcb200

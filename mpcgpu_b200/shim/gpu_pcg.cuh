@@ -83,10 +83,11 @@ template <typename T>
 size_t pcgSharedMemSize(uint32_t state_size, uint32_t knot_points) {
     size_t bytes = sizeof(T) * mpcb200_refstyle::smem_elems<T>(state_size);
     if (std::is_same<T, float>::value && state_size == 14 && mpcb200_shim::cluster_for(knot_points) != 0) {
-        const size_t slots = mpcb200_shim::KPC + 2;
         const size_t cl = mpcb200_shim::cluster_for(knot_points);
-        // == Cfg<16, cl, 8>::SMEM_BYTES (kept in closed form because knot_points is a run-time value here)
-        bytes = sizeof(float) * (slots * (624 + 196 + 20 + 20) + 4 * 20 + 2 * ((cl * 4 + 3) & ~size_t(3)) + 4);
+        // == Cfg<16, cl, 8>::SMEM_BYTES: knot_points is a run-time value here, and the cluster size only
+        // enters through the two partial-sum buffers (NREDP = cl * 4 warps, rounded up to 4)
+        using C1 = mpcb200::Cfg<mpcb200_shim::KPC, 1, 8>;
+        bytes = C1::SMEM_BYTES + sizeof(float) * 2 * (((cl * 4 + 3) & ~size_t(3)) - C1::NREDP);
     }
 #if MPCB200_SHIM_HAVE_DIMS
     // the reference launches with more than the 48 KB default and with cluster sizes up to 16:
