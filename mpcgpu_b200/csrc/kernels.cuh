@@ -92,19 +92,29 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
     {
         constexpr int TOT2 = CF::KPC * 3 * SS / 2, ITERS = (TOT2 + CF::NT - 1) / CF::NT;
         const float2* src = reinterpret_cast<const float2*>(Pg + (size_t)k0 * 3 * SS);
-#pragma unroll 8
-        for (int it = 0; it < ITERS; it++) {
-            const int e2 = threadIdx.x + it * CF::NT;
-            if (e2 < TOT2) {
+        constexpr int UN = 8;     // loads first, stores after: UN loads in flight per lane
+        for (int it0 = 0; it0 < ITERS; it0 += UN) {
+            float2 v[UN];
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const int e2 = threadIdx.x + (it0 + u) * CF::NT;
                 const int e = 2 * e2;
-                const int gg = e / (3 * SS), w = e - gg * 3 * SS;
-                const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
+                const int gg = e / (3 * SS), blk = (e - gg * 3 * SS) / SS;
                 const int kk = k0 + gg;
                 const bool corner = (kk == 0 && blk == 0 && !glob_l) || (kk == N - 1 && blk == 2 && !glob_r);
-                float2 v = make_float2(0.f, 0.f);
-                if (kk < N && !corner) v = __ldg(src + e2);
-                float* d = smem + CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j;
-                d[0] = v.x; d[CF::PR] = v.y;
+                v[u] = make_float2(0.f, 0.f);
+                if (it0 + u < ITERS && e2 < TOT2 && kk < N && !corner) v[u] = __ldg(src + e2);
+            }
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const int e2 = threadIdx.x + (it0 + u) * CF::NT;
+                if (it0 + u < ITERS && e2 < TOT2) {
+                    const int e = 2 * e2;
+                    const int gg = e / (3 * SS), w = e - gg * 3 * SS;
+                    const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
+                    float* d = smem + CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j;
+                    d[0] = v[u].x; d[CF::PR] = v[u].y;
+                }
             }
         }
     }

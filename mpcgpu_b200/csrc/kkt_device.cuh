@@ -287,19 +287,30 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     {
         constexpr int TOT2 = KPC * CSET / 2, ITERS = (TOT2 + CF::NT - 1) / CF::NT;
         const float2* src = reinterpret_cast<const float2*>(P.C + ((ptrdiff_t)k0 - 1) * CSET);
-#pragma unroll 8
-        for (int it = 0; it < ITERS; it++) {
-            const int i2 = tid + it * CF::NT;
-            if (i2 < TOT2) {
-                const int idx = 2 * i2;
-                const int gg = idx / CSET, e = idx - gg * CSET;
-                const int kk = k0 + gg;
-                float2 v = f2(0.f, 0.f);
-                if (kk >= 1 && kk < N) v = __ldg(src + i2);
-                if (e < SS) *reinterpret_cast<float2*>(TA + (gg + 1) * TK + e) = v;     // column-major A
-                else {
-                    const int m = (e - SS) / S, i = (e - SS) - m * S;
-                    *reinterpret_cast<float2*>(PW + (gg + 1) * PK + m * PR + cL + i) = v;
+        // loads first (branch-free, UN in flight per lane), stores after: with the store's branches
+        // in between the compiler keeps ONE load in flight and the CTA waits out ITERS HBM round trips
+        constexpr int UN = 8;
+        for (int it0 = 0; it0 < ITERS; it0 += UN) {
+            float2 v[UN];
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const int i2 = tid + (it0 + u) * CF::NT;
+                const int kk = k0 + (2 * i2) / CSET;
+                const bool ld = (it0 + u < ITERS) && i2 < TOT2 && kk >= 1 && kk < N;
+                v[u] = f2(0.f, 0.f);
+                if (ld) v[u] = __ldg(src + i2);
+            }
+#pragma unroll
+            for (int u = 0; u < UN; u++) {
+                const int i2 = tid + (it0 + u) * CF::NT;
+                if (it0 + u < ITERS && i2 < TOT2) {
+                    const int idx = 2 * i2;
+                    const int gg = idx / CSET, e = idx - gg * CSET;
+                    if (e < SS) *reinterpret_cast<float2*>(TA + (gg + 1) * TK + e) = v[u];     // column-major A
+                    else {
+                        const int m = (e - SS) / S, i = (e - SS) - m * S;
+                        *reinterpret_cast<float2*>(PW + (gg + 1) * PK + m * PR + cL + i) = v[u];
+                    }
                 }
             }
         }
