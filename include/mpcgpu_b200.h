@@ -125,6 +125,15 @@ int mpcgpu_b200_solver_solve_host_f32(mpcgpu_b200_solver* solver, uint32_t batch
                                       uint32_t max_iter, float exit_tol, uint32_t* h_iters,
                                       uint8_t* h_max_iter_exit, float* h_Ginv);
 
+/* Same with the warm start read from its own buffer: h_lambda0 (in) may differ from h_lambda (out);
+ * h_lambda0 == NULL is the cold start lambda0 = 0 of the first SQP iteration
+ * (include/mpcsim.cuh:201 zero-fills d_lambda): nothing is copied in for it. */
+int mpcgpu_b200_solver_solve_host_io_f32(mpcgpu_b200_solver* solver, uint32_t batch,
+                                         const float* h_G, const float* h_C, const float* h_g,
+                                         const float* h_c, float rho, const float* h_lambda0,
+                                         float* h_lambda, uint32_t max_iter, float exit_tol,
+                                         uint32_t* h_iters, uint8_t* h_max_iter_exit, float* h_Ginv);
+
 /* ---- long horizon split by knot range across the GPUs of one box (NEW: the reference has no
  * multi-GPU path; BASELINE.json configs[3]).  Rank r owns knots
  * [r*knots_local, (r+1)*knots_local) and holds only ITS slices of S / Pinv / gamma / lambda

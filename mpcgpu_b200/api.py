@@ -208,14 +208,18 @@ class HostSolver:
         return ctypes.c_void_p(t.data_ptr())
 
     def solve(self, h_G, h_C, h_g, h_c, rho, h_lambda, h_iters, h_exit, config: PcgConfig,
-              batch, h_Ginv=None):
+              batch, h_Ginv=None, h_lambda0="inplace"):
+        """h_lambda0: warm start; "inplace" (default) reads it from h_lambda, None = cold start
+        (lambda0 = 0, nothing copied in), or a separate host tensor."""
         z = sizes(self.s, self.c, self.N)
         f = torch.float32
-        rc = lib().mpcgpu_b200_solver_solve_host_f32(
+        lam0 = h_lambda if isinstance(h_lambda0, str) else h_lambda0
+        rc = lib().mpcgpu_b200_solver_solve_host_io_f32(
             self._h, ctypes.c_uint32(batch),
             self._hp(h_G, f, z["G"] * batch, "h_G"), self._hp(h_C, f, z["C"] * batch, "h_C"),
             self._hp(h_g, f, z["g"] * batch, "h_g"), self._hp(h_c, f, z["c"] * batch, "h_c"),
-            ctypes.c_float(rho), self._hp(h_lambda, f, z["lambda"] * batch, "h_lambda"),
+            ctypes.c_float(rho), self._hp(lam0, f, z["lambda"] * batch, "h_lambda0"),
+            self._hp(h_lambda, f, z["lambda"] * batch, "h_lambda"),
             ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
             self._hp(h_iters, torch.int32, batch, "h_iters"),
             self._hp(h_exit, torch.uint8, batch, "h_exit"),

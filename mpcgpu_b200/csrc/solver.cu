@@ -97,6 +97,15 @@ int mpcgpu_b200_solver_solve_host_f32(mpcgpu_b200_solver* S, uint32_t batch, con
                                       float rho, float* h_lambda, uint32_t max_iter,
                                       float exit_tol, uint32_t* h_iters, uint8_t* h_exit,
                                       float* h_Ginv) {
+    return mpcgpu_b200_solver_solve_host_io_f32(S, batch, h_G, h_C, h_g, h_c, rho, h_lambda, h_lambda, max_iter,
+                                                exit_tol, h_iters, h_exit, h_Ginv);
+}
+
+int mpcgpu_b200_solver_solve_host_io_f32(mpcgpu_b200_solver* S, uint32_t batch, const float* h_G,
+                                         const float* h_C, const float* h_g, const float* h_c,
+                                         float rho, const float* h_lambda0, float* h_lambda,
+                                         uint32_t max_iter, float exit_tol, uint32_t* h_iters,
+                                         uint8_t* h_exit, float* h_Ginv) {
     if (!S || batch < 1 || batch > S->max_batch || !h_G || (S->N > 1 && !h_C) || !h_g || !h_c ||
         !h_lambda || !h_iters || !h_exit)
         return (int)cudaErrorInvalidValue;
@@ -115,7 +124,8 @@ int mpcgpu_b200_solver_solve_host_f32(mpcgpu_b200_solver* S, uint32_t batch, con
         if (S->nC) CK(cudaMemcpyAsync(S->dC[b], h_C + first * S->nC, sizeof(float) * S->nC * k, cudaMemcpyHostToDevice, S->st_in));
         CK(cudaMemcpyAsync(S->dg[b], h_g + first * S->ng, sizeof(float) * S->ng * k, cudaMemcpyHostToDevice, S->st_in));
         CK(cudaMemcpyAsync(S->dc[b], h_c + first * S->nc, sizeof(float) * S->nc * k, cudaMemcpyHostToDevice, S->st_in));
-        CK(cudaMemcpyAsync(S->dlam[b], h_lambda + first * S->nv, sizeof(float) * S->nv * k, cudaMemcpyHostToDevice, S->st_in));
+        if (h_lambda0) CK(cudaMemcpyAsync(S->dlam[b], h_lambda0 + first * S->nv, sizeof(float) * S->nv * k, cudaMemcpyHostToDevice, S->st_in));
+        else CK(cudaMemsetAsync(S->dlam[b], 0, sizeof(float) * S->nv * k, S->st_in));   // cold start
         CK(cudaEventRecord(S->ev_in[b], S->st_in));
         CK(cudaStreamWaitEvent(S->st_k, S->ev_in[b], 0));
         int rc = mpcgpu_b200_kkt_solve_f32(S->s, S->c, S->N, (uint32_t)k, S->dG[b], S->dC[b], S->dg[b],

@@ -250,6 +250,13 @@ def test_host_solver_matches_device_path():
     hs.solve(hG, hC, hg, hc, d["rho"], hl, hi, he, cfg, B, h_Ginv=hGi)
     assert torch.equal(hl, lam.cpu()) and torch.equal(hi, it.cpu()) and torch.equal(he, ex.cpu())
     assert torch.equal(hGi, G.cpu())
+    # separate warm-start buffer, and the cold start (lambda0 = 0 without a copy): same answers
+    hl2 = torch.full((B, S * N), float("nan")).pin_memory()
+    hs.solve(hG, hC, hg, hc, d["rho"], hl2, hi, he, cfg, B, h_lambda0=torch.zeros((B, S * N)).pin_memory())
+    assert torch.equal(hl2, lam.cpu())
+    hl3 = torch.full((B, S * N), float("nan")).pin_memory()
+    hs.solve(hG, hC, hg, hc, d["rho"], hl3, hi, he, cfg, B, h_lambda0=None)
+    assert torch.equal(hl3, lam.cpu()) and torch.equal(hi, it.cpu())
     hs.close()
 
 
