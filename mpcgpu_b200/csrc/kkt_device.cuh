@@ -289,7 +289,9 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
         const float2* src = reinterpret_cast<const float2*>(P.C + ((ptrdiff_t)k0 - 1) * CSET);
         // loads first (branch-free, UN in flight per lane), stores after: with the store's branches
         // in between the compiler keeps ONE load in flight and the CTA waits out ITERS HBM round trips
-        constexpr int UN = 8;
+        // latency tilings (<= 20 float2 per lane): the whole tile in flight at once; the 64-knot
+        // throughput tiling measured best with 8 (1.23M vs 1.21M solves/s with all 37)
+        constexpr int UN = ITERS <= 20 ? ITERS : 8;
         for (int it0 = 0; it0 < ITERS; it0 += UN) {
             float2 v[UN];
 #pragma unroll
