@@ -119,6 +119,39 @@ def _graph_time_us(torch, fn, reset, reps=20):
     return e0.elapsed_time(e1) / reps * 1e3
 
 
+def two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, tol, peak):
+    """The two kernels of the reference's own structure (S, Pinv materialised in HBM, Def. A) on the
+    same batch: each against the HBM roofline with its algorithmic bytes."""
+    S, C = 14, 7
+    dev = G0.device
+    z = mg.sizes(S, C, N)
+    G = G0.clone()
+    Sg = torch.empty((B, z["S"]), device=dev); Pg = torch.empty_like(Sg)
+    gam = torch.empty((B, z["gamma"]), device=dev)
+    lam = torch.zeros((B, S * N), device=dev)
+    it = torch.zeros(B, dtype=torch.int32, device=dev); ex = torch.ones(B, dtype=torch.uint8, device=dev)
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    ts, tp = [], []
+    for rep in range(6):
+        G.copy_(G0); lam.zero_()
+        a0, a1, b1 = ev(), ev(), ev()
+        a0.record()
+        mg.form_schur_system(S, C, N, G, Cm, g, cv, Sg, Pg, gam, rho, batch=B)
+        a1.record()
+        mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, cfg, batch=B)
+        b1.record()
+        torch.cuda.synchronize()
+        if rep >= 2:
+            ts.append(a0.elapsed_time(a1)); tp.append(a1.elapsed_time(b1))
+    ms_s, ms_p = float(np.mean(ts)), float(np.mean(tp))
+    by_s, by_p = B * (8036 * N - 1596), B * 4872 * N
+    return {"schur_kernel": {"ms": ms_s, "bytes": by_s, "GBps": by_s / ms_s / 1e6, "frac_hbm": by_s / ms_s / 1e6 / peak},
+            "pcg_kernel": {"ms": ms_p, "bytes": by_p, "GBps": by_p / ms_p / 1e6, "frac_hbm": by_p / ms_p / 1e6 / peak,
+                           "mean_iters": float(it.float().mean().item())},
+            "two_stage_solves_per_s": B / ((ms_s + ms_p) * 1e-3)}
+
+
 def single_solve_latency(torch, mg, N, tol):
     """Single-instance latency (BASELINE.json metric (i)), GPU-bound (CUDA-graph replay): PCG only
     (cluster kernel vs the reference-STYLE 4-grid-barrier kernel, our restatement of the absent
@@ -348,6 +381,7 @@ def main():
                                     "sample": "%d instances x 3 passes; oracle Schur restatement (share %.2f) + reference QDLDL"
                                               % (sample, r["schur_share"])}
             if not a.no_extras:
+                line["two_stage"] = two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, a.tol, peak)
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
         if ks is not None:
             line["knot_split"] = ks
