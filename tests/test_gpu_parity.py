@@ -293,3 +293,40 @@ def test_compute_dz_matches_oracle_standalone_and_as_epilogue(N):
         ref32 = oracle.dz(S, C, N, Gi[b], d["C"][b], d["g"][b], lam_h[b], np.float32)
         ref64 = oracle.dz(S, C, N, Gi[b], d["C"][b], d["g"][b], lam_h[b], np.float64)
         assert rel(dz_h[b], ref64) < max(1e-4, 4.0 * rel(ref32, ref64))
+
+
+@pytest.mark.parametrize("N,B", [(1, 2), (5, 3), (33, 2), (64, 300), (100, 3), (512, 1)])
+def test_kernels_write_only_their_outputs(N, B):
+    """Every output buffer sits between two sentinel guards (and inputs are compared with their
+    originals afterwards): nothing outside [buffer, buffer + size) may change, for ragged N (not a
+    multiple of the knots per CTA), single-knot problems and batches larger than one wave."""
+    z = mg.sizes(S, C, N)
+    d = synth.gen_kkt_fast(N, B, seed=4242 + N)
+    GUARD, SENT = 256, -12345.5
+
+    def guarded(n, dtype=torch.float32, sent=SENT):
+        buf = torch.full((n + 2 * GUARD,), sent, dtype=dtype, device=DEV)
+        return buf, buf[GUARD:GUARD + n]
+
+    def intact(buf, n, sent=SENT):
+        return bool((buf[:GUARD] == sent).all()) and bool((buf[GUARD + n:] == sent).all())
+
+    Gb, G = guarded(B * z["G"]); G.copy_(dev(d["G"]).reshape(-1))
+    Cm, g, cv = dev(d["C"]), dev(d["g"]), dev(d["c"])
+    C0, g0, c0 = Cm.clone(), g.clone(), cv.clone()
+    Sb, Sg = guarded(B * z["S"]); Pb, Pg = guarded(B * z["S"]); gb, gam = guarded(B * z["gamma"])
+    lb, lam = guarded(B * S * N); lam.zero_()
+    db, dz = guarded(B * z["g"])
+    ib, it = guarded(B, torch.int32, -7); eb, ex = guarded(B, torch.uint8, 77)
+    cfg = mg.PcgConfig(pcg_exit_tol=1e-4)
+    v = lambda t, n: t.view(B, n)
+    mg.form_schur_system(S, C, N, v(G, z["G"]), Cm, g, cv, v(Sg, z["S"]), v(Pg, z["S"]), v(gam, z["gamma"]), d["rho"], batch=B)
+    mg.pcg(S, N, v(Sg, z["S"]), v(Pg, z["S"]), v(gam, z["gamma"]), v(lam, S * N), it, ex, cfg, batch=B)
+    mg.compute_dz(S, C, N, v(G, z["G"]), Cm, g, v(lam, S * N), v(dz, z["g"]), batch=B)
+    G.copy_(dev(d["G"]).reshape(-1)); lam.zero_()
+    mg.kkt_solve_dz(S, C, N, v(G, z["G"]), Cm, g, cv, d["rho"], v(lam, S * N), v(dz, z["g"]), it, ex, cfg, batch=B)
+    torch.cuda.synchronize()
+    assert intact(Gb, B * z["G"]) and intact(Sb, B * z["S"]) and intact(Pb, B * z["S"]) and intact(gb, B * z["gamma"])
+    assert intact(lb, B * S * N) and intact(db, B * z["g"]) and intact(ib, B, -7) and intact(eb, B, 77)
+    assert torch.equal(Cm, C0) and torch.equal(g, g0) and torch.equal(cv, c0)
+    assert bool(torch.isfinite(lam).all()) and bool(torch.isfinite(dz).all()) and int(ex.sum()) == 0
