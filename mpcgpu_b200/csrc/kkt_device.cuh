@@ -605,28 +605,43 @@ __device__ __forceinline__ float cluster_sum(float* red, uint64_t* mb, unsigned 
         if (lane == 0) *slot = w;
         __syncthreads();
         const float4* r4 = reinterpret_cast<const float4*>(red + buf * CF::NREDP);
-        float acc = 0.f;
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);      // four interleaved chains, fixed order
 #pragma unroll
         for (int q = 0; q < CF::NREDP / 4; q++) {
             const float4 v = r4[q];
-            acc += v.x;
-            if (4 * q + 1 < NRED) acc += v.y;
-            if (4 * q + 2 < NRED) acc += v.z;
-            if (4 * q + 3 < NRED) acc += v.w;
+            acc.x += v.x;
+            if (4 * q + 1 < NRED) acc.y += v.y;
+            if (4 * q + 2 < NRED) acc.z += v.z;
+            if (4 * q + 3 < NRED) acc.w += v.w;
         }
-        return acc;
+        return (acc.x + acc.y) + (acc.z + acc.w);
     } else {
         if (threadIdx.x == 0) mbar_arrive_expect_tx(mb + buf, (unsigned)NRED * 4u + halo_bytes);
         if (lane < CL) st_async_f32(mapa_u32(smem_u32(slot), (unsigned)lane), w, mapa_u32(smem_u32(mb + buf), (unsigned)lane));
         mbar_wait(mb + buf, par[buf]);
         par[buf] ^= 1u;
-        float acc = 0.f;
+        const float4* r4 = reinterpret_cast<const float4*>(red + buf * CF::NREDP);
+        if constexpr (NRED <= 64) {
+            // every lane adds all NRED partials itself (broadcast LDS.128, four interleaved chains, fixed
+            // order -> the same bits in every lane of every CTA): shorter than a second 5-level shuffle
+            // tree (measured N=128, CL=8: 1.74 -> 1.35 us per iteration)
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int q = 0; q < (NRED + 31) / 32; q++) {
-            const int idx = lane + 32 * q;
-            if (idx < NRED) acc += red[buf * CF::NREDP + idx];
+            for (int q = 0; q < CF::NREDP / 4; q++) {
+                const float4 v = r4[q];
+                acc.x += v.x;
+                if (4 * q + 1 < NRED) acc.y += v.y;
+                if (4 * q + 2 < NRED) acc.z += v.z;
+                if (4 * q + 3 < NRED) acc.w += v.w;
+            }
+            return (acc.x + acc.y) + (acc.z + acc.w);
+        } else {
+            // many partials (CL = 16 with 8 warps): one float4 per lane, then the butterfly
+            static_assert(NRED % 4 == 0 && NRED <= 128, "one float4 per lane");
+            float acc = 0.f;
+            if (lane < NRED / 4) { const float4 v = r4[lane]; acc = (v.x + v.y) + (v.z + v.w); }
+            return warp_sum(acc);
         }
-        return warp_sum(acc);
     }
 }
 
