@@ -330,3 +330,32 @@ def test_kernels_write_only_their_outputs(N, B):
     assert intact(lb, B * S * N) and intact(db, B * z["g"]) and intact(ib, B, -7) and intact(eb, B, 77)
     assert torch.equal(Cm, C0) and torch.equal(g, g0) and torch.equal(cv, c0)
     assert bool(torch.isfinite(lam).all()) and bool(torch.isfinite(dz).all()) and int(ex.sum()) == 0
+
+
+@pytest.mark.parametrize("N,refstyle", [(8, False), (64, False), (128, False), (512, False), (64, True)])
+def test_pcg_degenerate_exits_match_oracle(N, refstyle):
+    """Exit paths of the iteration: max_iter = 0 (lambda untouched, 0 iterations, flag
+    set), zero right-hand side with a zero start (p.Sp = 0 on the first iteration), a start that
+    already satisfies |r.Pinv r| < tol."""
+    d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + 13 * N)
+    S32, P32, g32, _ = oracle.schur(S, C, N, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], np.float32)
+    Sd, Pd, gd = dev(S32[None]), dev(P32[None]), dev(g32[None])
+    rng = np.random.default_rng(7 * N)
+    start = rng.standard_normal((1, S * N)).astype(np.float32)
+    # max_iter = 0
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S32, P32, g32, start[0], 0, 1e-4)
+    lam_g, it_g, ex_g = gpu_pcg(N, Sd, Pd, gd, start, 1e-4, max_iter=0, refstyle=refstyle)
+    assert int(it_g[0]) == it_o == 0 and bool(ex_g[0]) == ex_o
+    assert np.array_equal(lam_g[0], start[0]) and np.array_equal(lam_o, start[0])
+    # gamma = 0, lambda0 = 0
+    zero_g = dev(np.zeros((1, S * N), np.float32))
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S32, P32, 0 * g32, np.zeros(S * N, np.float32), 100, 1e-4)
+    lam_g, it_g, ex_g = gpu_pcg(N, Sd, Pd, zero_g, np.zeros((1, S * N), np.float32), 1e-4, max_iter=100, refstyle=refstyle)
+    assert int(it_g[0]) == it_o and bool(ex_g[0]) == ex_o
+    assert np.array_equal(lam_g[0], np.zeros(S * N, np.float32)) and not np.any(lam_o)
+    # converged start: one more solve from the converged lambda stops at once
+    lam_c, _, _ = gpu_pcg(N, Sd, Pd, gd, np.zeros((1, S * N), np.float32), 1e-4, refstyle=refstyle)
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S32, P32, g32, lam_c[0], 100, 1e-2)
+    lam_g, it_g, ex_g = gpu_pcg(N, Sd, Pd, gd, lam_c, 1e-2, max_iter=100, refstyle=refstyle)
+    assert abs(int(it_g[0]) - it_o) <= 1 and it_o <= 1 and bool(ex_g[0]) == ex_o
+    assert rel(lam_g[0], lam_o) < 1e-4
