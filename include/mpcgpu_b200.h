@@ -91,6 +91,16 @@ int mpcgpu_b200_kkt_solve_dz_f32(uint32_t state_size, uint32_t control_size, uin
                                  uint32_t max_iter, float exit_tol, uint32_t* d_iters,
                                  uint8_t* d_max_iter_exit, void* d_ws, void* stream);
 
+/* The same with rho read from device memory (one float, shared by the batch) when the kernel
+ * runs: every argument is then fixed, so the launch can be captured once into a CUDA graph and
+ * replayed per SQP iteration while rho adapts (include/pcg/sqp.cuh:392-393,412-413). */
+int mpcgpu_b200_kkt_solve_dz_dev_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                                     uint32_t batch, float* d_G, const float* d_C, const float* d_g,
+                                     const float* d_c, const float* d_rho, float* d_lambda,
+                                     float* d_dz, uint32_t max_iter, float exit_tol,
+                                     uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws,
+                                     void* stream);
+
 /* compute_dz alone (include/common/dz.cuh:124-133): d_Ginv = d_G after mpcgpu_b200_schur_f32 /
  * kkt_solve, d_C, d_g as given to them, d_lambda the multipliers.  Batched like the rest. */
 int mpcgpu_b200_dz_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,

@@ -21,6 +21,7 @@ struct BatchArgs {
     unsigned max_iter; float exit_tol;
     unsigned* iters; uint8_t* exits;
     float* dz = nullptr; size_t sdz = 0;   // optional compute_dz epilogue (fused) / output of dz_kernel
+    const float* rho_dev = nullptr;        // optional: rho read from device memory (launches replayed from a CUDA graph)
 };
 
 // PROW column offset of block column `blk` (0 left, 1 diag, 2 right) of the reference layout
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a
     const int b = blockIdx.x / CF::CL;
     KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
     Rows<CF::RPT> R;
-    schur_rows<CF>(smem, P, a.N, a.rho, R);
+    schur_rows<CF>(smem, P, a.N, a.rho_dev ? __ldg(a.rho_dev) : a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
     if (a.dz) {   // compute_dz epilogue: lambda and G^-1 were written by this cluster, read back through L2

@@ -13,7 +13,11 @@
 //   * every buffer, stream and pinned mailbox lives in a workspace built on the first call and
 //     kept (the reference slot does ~20 cudaMalloc/cudaFree, 8 stream creates and a cuBLAS
 //     handle per SQP solve, inside its own 2 ms budget);
-//   * the accepted step xu += alpha dz is a 1-block kernel instead of a cuBLAS call.
+//   * the accepted step xu += alpha dz is a 1-block kernel instead of a cuBLAS call;
+//   * one SQP iteration (step, KKT blocks, solve + dz, the 8 line-search kernels on 8 streams, the
+//     read-backs) is captured ONCE into a CUDA graph and replayed: one graph launch and one stream
+//     synchronise per iteration; rho and the step length enter through a pinned 8-byte control word
+//     (MPCGPU_B200_SLOT_GRAPH=0, FINE_GRAINED_TIMING or TIME_LINSYS select the plain stream path).
 // The dynamics-facing kernels are the reference's own, included from where they are:
 // generate_kkt_submatrices (common/kkt.cuh), compute_merit and ls_gato_compute_merit
 // (common/merit.cuh).  fp32 only (settings.cuh USE_DOUBLES 0).
@@ -51,6 +55,15 @@ __global__ void take_step(uint32_t n, T alpha, const T* __restrict__ dz, T* __re
         xu[i] += alpha * dz[i];
 }
 
+// graph replay: the step length lives in device memory; 0 = the last line search found no step
+template <typename T>
+__global__ void take_step_dev(uint32_t n, const T* __restrict__ alpha_dev, const T* __restrict__ dz, T* __restrict__ xu) {
+    const T alpha = *alpha_dev;
+    if (alpha == T(0)) return;
+    for (uint32_t i = threadIdx.x + blockIdx.x * blockDim.x; i < n; i += blockDim.x * gridDim.x)
+        xu[i] += alpha * dz[i];
+}
+
 // What one (state_size, control_size, knot_points) needs on the device, carved out of a single
 // allocation; pinned host words for everything the host reads back.
 template <typename T>
@@ -61,7 +74,17 @@ struct Workspace {
     T *merit0 = nullptr, *merits = nullptr, *merit_tmp = nullptr;
     uint32_t* iters = nullptr;   // [SQP_MAX_ITER]
     uint8_t*  flags = nullptr;   // [SQP_MAX_ITER]
-    struct Host { T merit0; T merits[kAlphas]; uint32_t iters[SQP_MAX_ITER]; uint8_t flags[SQP_MAX_ITER]; };
+    struct Host { T merit0; T merits[kAlphas]; uint32_t iters[SQP_MAX_ITER]; uint8_t flags[SQP_MAX_ITER]; T ctl[2]; };
+    T* ctl = nullptr;            // device copy of Host::ctl = {rho, step length}
+    // the captured SQP iteration and the arguments it was captured for
+    cudaStream_t main = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join[kAlphas] = {};
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    bool graph_failed = false;
+    const void* key_ptr[4] = {nullptr, nullptr, nullptr, nullptr};
+    float key_dt = 0.f, key_tol = 0.f;
+    uint32_t key_iter = 0;
     Host* h = nullptr;
     cudaStream_t ls_stream[kAlphas] = {};
     uint32_t nz = 0;             // length of xu / dz
@@ -76,21 +99,34 @@ struct Workspace {
                      ng = nz, nc = size_t(s) * N;
         const size_t sz[] = {nG * sizeof(T), nC * sizeof(T), ng * sizeof(T), nc * sizeof(T), size_t(nz) * sizeof(T),
                              s * sizeof(T), sizeof(T), kAlphas * sizeof(T), size_t(kAlphas) * N * sizeof(T),
-                             SQP_MAX_ITER * sizeof(uint32_t), SQP_MAX_ITER * sizeof(uint8_t)};
-        size_t off[12] = {0};
-        for (int i = 0; i < 11; i++) off[i + 1] = off[i] + up(sz[i]);
-        gpuErrchk(cudaMalloc(&d_pool, off[11]));
-        gpuErrchk(cudaMemset(d_pool, 0, off[11]));
+                             SQP_MAX_ITER * sizeof(uint32_t), SQP_MAX_ITER * sizeof(uint8_t), 2 * sizeof(T)};
+        size_t off[13] = {0};
+        for (int i = 0; i < 12; i++) off[i + 1] = off[i] + up(sz[i]);
+        gpuErrchk(cudaMalloc(&d_pool, off[12]));
+        gpuErrchk(cudaMemset(d_pool, 0, off[12]));
+        ctl = (T*)(d_pool + off[11]);
         G = (T*)(d_pool + off[0]);  C = (T*)(d_pool + off[1]);  g = (T*)(d_pool + off[2]);
         cv = (T*)(d_pool + off[3]); dz = (T*)(d_pool + off[4]); xs = (T*)(d_pool + off[5]);
         merit0 = (T*)(d_pool + off[6]); merits = (T*)(d_pool + off[7]); merit_tmp = (T*)(d_pool + off[8]);
         iters = (uint32_t*)(d_pool + off[9]); flags = (uint8_t*)(d_pool + off[10]);
         gpuErrchk(cudaMallocHost(&h, sizeof(Host)));
         for (uint32_t i = 0; i < kAlphas; i++) gpuErrchk(cudaStreamCreate(&ls_stream[i]));
+        // blocking streams: ordered against the caller's legacy-stream work like the reference's own
+        gpuErrchk(cudaStreamCreate(&main));
+        gpuErrchk(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+        for (uint32_t i = 0; i < kAlphas; i++) gpuErrchk(cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming));
+    }
+    void drop_graph() {
+        if (exec) cudaGraphExecDestroy(exec);
+        if (graph) cudaGraphDestroy(graph);
+        exec = nullptr; graph = nullptr;
     }
     void release() {
         if (!d_pool) return;
-        for (uint32_t i = 0; i < kAlphas; i++) cudaStreamDestroy(ls_stream[i]);
+        drop_graph();
+        for (uint32_t i = 0; i < kAlphas; i++) { cudaStreamDestroy(ls_stream[i]); cudaEventDestroy(ev_join[i]); }
+        cudaEventDestroy(ev_fork); cudaStreamDestroy(main);
+        graph_failed = false;
         cudaFreeHost(h); cudaFree(d_pool);
         d_pool = nullptr; h = nullptr;
     }
@@ -156,7 +192,93 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
     T merit_now = 0, drho = 1;
     const T rho_factor = RHO_FACTOR, rho_max = RHO_MAX, rho_min = RHO_MIN;
 
-    for (uint32_t it = 0; it < SQP_MAX_ITER; it++) {
+    // ---- graph path: one captured SQP iteration, replayed ---------------------------------------
+    static const bool want_graph = [] { const char* e = getenv("MPCGPU_B200_SLOT_GRAPH"); return !(e && e[0] == '0'); }();
+    bool use_graph = want_graph && !fine && !time_linsys && !w.graph_failed;
+    if (use_graph) {
+        const void* key[4] = {d_eePos_traj, d_lambda, d_xu, d_dynMem_const};
+        const bool same = w.exec && key[0] == w.key_ptr[0] && key[1] == w.key_ptr[1] && key[2] == w.key_ptr[2] &&
+                          key[3] == w.key_ptr[3] && w.key_dt == timestep && w.key_tol == config.pcg_exit_tol &&
+                          w.key_iter == config.pcg_max_iter;
+        if (!same) {
+            w.drop_graph();
+            bool ok = cudaStreamBeginCapture(w.main, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+            if (ok) {
+                ok &= cudaMemcpyAsync(w.ctl, w.h->ctl, 2 * sizeof(T), cudaMemcpyHostToDevice, w.main) == cudaSuccess;
+                take_step_dev<T><<<1, 256, 0, w.main>>>(w.nz, w.ctl + 1, w.dz, d_xu);
+                generate_kkt_submatrices<T><<<knot_points, KKT_THREADS, kkt_smem, w.main>>>(
+                    state_size, control_size, knot_points, w.G, w.C, w.g, w.cv, d_dynMem_const, dt, d_eePos_traj, w.xs, d_xu);
+                ok &= mpcgpu_b200_kkt_solve_dz_dev_f32(state_size, control_size, knot_points, 1, w.G, w.C, w.g, w.cv, w.ctl,
+                                                       d_lambda, w.dz, config.pcg_max_iter, config.pcg_exit_tol, w.iters,
+                                                       w.flags, nullptr, (void*)w.main) == 0;
+                ok &= cudaEventRecord(w.ev_fork, w.main) == cudaSuccess;
+                for (uint32_t p = 0; p < kAlphas; p++) {
+                    void* args[] = {&ks, &kc, &kn, &w.xs, &d_xu, &d_eePos_traj, &mu, &dt, &d_dynMem_const, &w.dz, &p,
+                                    &w.merits, &w.merit_tmp};
+                    ok &= cudaStreamWaitEvent(w.ls_stream[p], w.ev_fork, 0) == cudaSuccess;
+                    ok &= cudaLaunchCooperativeKernel(ls_kernel, knot_points, MERIT_THREADS, args, ls_smem, w.ls_stream[p]) == cudaSuccess;
+                    ok &= cudaEventRecord(w.ev_join[p], w.ls_stream[p]) == cudaSuccess;
+                    ok &= cudaStreamWaitEvent(w.main, w.ev_join[p], 0) == cudaSuccess;
+                }
+                ok &= cudaMemcpyAsync(w.h->merits, w.merits, kAlphas * sizeof(T), cudaMemcpyDeviceToHost, w.main) == cudaSuccess;
+                ok &= cudaMemcpyAsync(&w.h->iters[0], w.iters, sizeof(uint32_t), cudaMemcpyDeviceToHost, w.main) == cudaSuccess;
+                ok &= cudaMemcpyAsync(&w.h->flags[0], w.flags, sizeof(uint8_t), cudaMemcpyDeviceToHost, w.main) == cudaSuccess;
+                ok &= cudaStreamEndCapture(w.main, &w.graph) == cudaSuccess && w.graph != nullptr;
+                ok = ok && cudaGraphInstantiate(&w.exec, w.graph, 0) == cudaSuccess;
+            }
+            if (!ok) {   // capture not possible here (e.g. cooperative launches): plain streams from now on
+                cudaGetLastError();
+                w.drop_graph();
+                w.graph_failed = true;
+                use_graph = false;
+            } else {
+                for (int i = 0; i < 4; i++) w.key_ptr[i] = key[i];
+                w.key_dt = timestep; w.key_tol = config.pcg_exit_tol; w.key_iter = config.pcg_max_iter;
+            }
+        }
+    }
+    if (use_graph) {
+        T pending = 0;                       // accepted step, applied by the next replay (or after the loop)
+        double iter_us = 0.0;                // duration of the last replay: do not start one that cannot finish
+        for (uint32_t it = 0; it < SQP_MAX_ITER; it++) {
+#if CONST_UPDATE_FREQ
+            clock_gettime(CLOCK_MONOTONIC, &t_now);
+            if (us_between(t_begin, t_now) + iter_us > SQP_MAX_TIME_US) break;
+#endif
+            timespec r0, r1;
+            clock_gettime(CLOCK_MONOTONIC, &r0);
+            w.h->ctl[0] = rho; w.h->ctl[1] = pending; pending = 0;
+            gpuErrchk(cudaGraphLaunch(w.exec, w.main));
+            gpuErrchk(cudaStreamSynchronize(w.main));
+            clock_gettime(CLOCK_MONOTONIC, &r1);
+            iter_us = us_between(r0, r1);
+            pcg_iter_vec.push_back(int(w.h->iters[0]));
+            pcg_exit_vec.push_back(w.h->flags[0] != 0);
+            if (!merit0_home) { merit_now = w.h->merit0; merit0_home = true; }
+            uint32_t best = 0;
+            T best_merit = merit_now;
+            for (uint32_t i = 0; i < kAlphas; i++)
+                if (w.h->merits[i] < best_merit) { best_merit = w.h->merits[i]; best = i; }
+            if (best_merit == merit_now) {
+                drho = max(drho * rho_factor, rho_factor);
+                rho = max(rho * drho, rho_min);
+                sqp_iter++;
+                if (rho > rho_max) { sqp_time_exit = false; rho = rho_reset; break; }
+                continue;
+            }
+            drho = min(drho / rho_factor, 1 / rho_factor);
+            rho = max(rho * drho, rho_min);
+            pending = T(-1.0) / T(1u << best);
+            sqp_iter++;
+            merit_now = best_merit;
+        }
+        if (pending != T(0)) {
+            take_step<T><<<1, 256, 0, w.main>>>(w.nz, pending, w.dz, d_xu);
+            gpuErrchk(cudaPeekAtLastError());
+        }
+    }
+
+    for (uint32_t it = 0; !use_graph && it < SQP_MAX_ITER; it++) {
         // 1. linearise: G, C, g, c
         lap_begin(fine);
         generate_kkt_submatrices<T><<<knot_points, KKT_THREADS, kkt_smem>>>(state_size, control_size, knot_points, w.G,
@@ -220,7 +342,7 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
     gpuErrchk(cudaDeviceSynchronize());   // also lands every asynchronous read-back
     timespec t_end;
     clock_gettime(CLOCK_MONOTONIC, &t_end);
-    for (uint32_t i = 0; i < solves; i++) {
+    for (uint32_t i = 0; i < solves; i++) {          // stream path: the asynchronous read-backs have landed
         pcg_iter_vec.push_back(int(w.h->iters[i]));
         pcg_exit_vec.push_back(w.h->flags[i] != 0);
     }
