@@ -45,8 +45,15 @@ struct Use {
     static constexpr uint32_t DIM = CLUSTER ? CL : 1;
 };
 
+// The caller's cooperative launch needs all N CTAs of its grid co-resident (as N / cluster whole
+// clusters), surplus ones included.  The driver schedules a kernel that holds tensor memory one CTA
+// per SM (measured on B200, tools/occupancy_probe.cu: 148 CTAs, 15 clusters of 8, 7 of 16), so the
+// Pinv rows go to tensor memory only while the grid fits that way (N <= 64); longer horizons keep
+// them in shared memory (3 CTAs per SM).
+__host__ __device__ constexpr int tmem_for(uint32_t N) { return N <= 64 ? MPCB200_PINV_TMEM : 0; }
+
 template <uint32_t N>
-using Tiling = mpcb200::Cfg<KPC, (cluster_for(N) ? cluster_for(N) : 1), 8>;
+using Tiling = mpcb200::Cfg<KPC, (cluster_for(N) ? cluster_for(N) : 1), 8, tmem_for(N)>;
 
 }  // namespace mpcb200_shim
 
