@@ -27,8 +27,8 @@
  *   - return value: 0 on success, otherwise a cudaError_t value
  *     (cudaErrorInvalidValue for unsupported sizes); mpcgpu_b200_last_error() has the text.
  *   - supported sizes in this build: state_size 14, control_size 7 (Kuka IIWA,
- *     examples/track_iiwa_pcg.cu:16-17), 1 <= knot_points <= 512, fp32
- *     (linsys_t, include/common/settings.cuh:49-57).
+ *     examples/track_iiwa_pcg.cu:16-17); fp32 (linsys_t, include/common/settings.cuh:49-57)
+ *     with 1 <= knot_points <= 512, and fp64 (USE_DOUBLES 1) with 1 <= knot_points <= 256.
  * There is NO CPU fallback: without a CUDA device every compute entry point fails.
  */
 #ifndef MPCGPU_B200_H
@@ -106,6 +106,34 @@ int mpcgpu_b200_kkt_solve_dz_dev_f32(uint32_t state_size, uint32_t control_size,
 int mpcgpu_b200_dz_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
                        uint32_t batch, const float* d_Ginv, const float* d_C, const float* d_g,
                        const float* d_lambda, float* d_dz, void* stream);
+
+/* ---- fp64 twins (linsys_t = double when include/common/settings.cuh:49-57 is built with
+ * USE_DOUBLES 1).  Same buffers, layouts, semantics and error behaviour as the _f32 entry points
+ * above with every float replaced by double; the same cluster kernels instantiated for double
+ * (16 knots per 256-thread CTA, S rows in registers, Pinv rows in shared memory, DFMA pairs).
+ * Supported sizes: state_size 14, control_size 7, 1 <= knot_points <= 256 (16 CTAs per cluster). */
+int mpcgpu_b200_schur_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                          uint32_t batch, double* d_G, const double* d_C, const double* d_g,
+                          const double* d_c, double rho, double* d_S, double* d_Pinv,
+                          double* d_gamma, void* stream);
+int mpcgpu_b200_pcg_f64(uint32_t state_size, uint32_t knot_points, uint32_t batch,
+                        const double* d_S, const double* d_Pinv, const double* d_gamma,
+                        double* d_lambda, uint32_t max_iter, double exit_tol, uint32_t* d_iters,
+                        uint8_t* d_max_iter_exit, void* d_ws, void* stream);
+int mpcgpu_b200_kkt_solve_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                              uint32_t batch, double* d_G, const double* d_C, const double* d_g,
+                              const double* d_c, double rho, double* d_lambda, uint32_t max_iter,
+                              double exit_tol, uint32_t* d_iters, uint8_t* d_max_iter_exit,
+                              void* d_ws, void* stream);
+/* d_dz may be NULL (no compute_dz epilogue). */
+int mpcgpu_b200_kkt_solve_dz_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                                 uint32_t batch, double* d_G, const double* d_C, const double* d_g,
+                                 const double* d_c, double rho, double* d_lambda, double* d_dz,
+                                 uint32_t max_iter, double exit_tol, uint32_t* d_iters,
+                                 uint8_t* d_max_iter_exit, void* d_ws, void* stream);
+int mpcgpu_b200_dz_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                       uint32_t batch, const double* d_Ginv, const double* d_C, const double* d_g,
+                       const double* d_lambda, double* d_dz, void* stream);
 
 /* Reference-STYLE PCG (one CTA per knot, 4 grid barriers per iteration, cooperative launch):
  * our restatement of the reference kernel's structure, kept as the in-repo

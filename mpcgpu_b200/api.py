@@ -64,6 +64,16 @@ def _ptr(t, dtype, what, numel=None):
     return ctypes.c_void_p(t.data_ptr())
 
 
+def _prec(t, what):
+    """linsys_t of a call = dtype of its matrices: float32 (settings.cuh USE_DOUBLES 0) -> the _f32 entry
+    points, float64 (USE_DOUBLES 1) -> the _f64 twins.  Returns (dtype, suffix, ctypes scalar type)."""
+    if isinstance(t, torch.Tensor) and t.dtype == torch.float64:
+        return torch.float64, "f64", ctypes.c_double
+    if isinstance(t, torch.Tensor) and t.dtype == torch.float32:
+        return torch.float32, "f32", ctypes.c_float
+    raise MpcGpuError("%s must be a float32 or float64 CUDA tensor" % what)
+
+
 def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -87,16 +97,17 @@ class PcgConfig:
 
 def form_schur_system(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, d_c,
                       d_S, d_Pinv, d_gamma, rho, batch=1):
-    """form_schur_system<float>: writes d_S, d_Pinv, d_gamma; d_G_dense becomes G^-1."""
+    """form_schur_system<T>: writes d_S, d_Pinv, d_gamma; d_G_dense becomes G^-1.
+    T = float / double by the dtype of d_G_dense."""
     s, c, N = state_size, control_size, knot_points
     z = sizes(s, c, N)
-    f = torch.float32
-    rc = lib().mpcgpu_b200_schur_f32(
+    f, sfx, cT = _prec(d_G_dense, "d_G_dense")
+    rc = getattr(lib(), "mpcgpu_b200_schur_" + sfx)(
         ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
         _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
         _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
         _ptr(d_g, f, "d_g", z["g"] * batch), _ptr(d_c, f, "d_c", z["c"] * batch),
-        ctypes.c_float(rho), _ptr(d_S, f, "d_S", z["S"] * batch),
+        cT(rho), _ptr(d_S, f, "d_S", z["S"] * batch),
         _ptr(d_Pinv, f, "d_Pinv", z["S"] * batch), _ptr(d_gamma, f, "d_gamma", z["gamma"] * batch),
         _stream())
     _check(rc, "form_schur_system")
@@ -108,18 +119,18 @@ def pcg(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_pcg_iters, d_
     d_pcg_iters: uint32 (int32 tensor storage), d_pcg_exit: uint8/bool tensor."""
     s, N = state_size, knot_points
     z = sizes(s, 7, N)
-    f = torch.float32
+    f, sfx, cT = _prec(d_S, "d_S")
     if d_pcg_iters.dtype != torch.int32 or d_pcg_exit.dtype not in (torch.uint8, torch.bool):
         raise MpcGpuError("d_pcg_iters must be int32 and d_pcg_exit uint8/bool")
     args = [_ptr(d_S, f, "d_S", z["S"] * batch), _ptr(d_Pinv, f, "d_Pinv", z["S"] * batch),
             _ptr(d_gamma, f, "d_gamma", z["gamma"] * batch),
             _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
-            ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+            ctypes.c_uint32(config.pcg_max_iter), cT(config.pcg_exit_tol),
             _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", batch),
             _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", batch)]
     if refstyle:
-        if batch != 1:
-            raise MpcGpuError("reference-style kernel is single-instance")
+        if batch != 1 or sfx != "f32":
+            raise MpcGpuError("reference-style kernel is single-instance, fp32")
         need = lib().mpcgpu_b200_workspace_bytes(ctypes.c_uint32(s), ctypes.c_uint32(7),
                                                  ctypes.c_uint32(N), ctypes.c_uint32(1))
         if d_ws is None:
@@ -127,8 +138,8 @@ def pcg(state_size, knot_points, d_S, d_Pinv, d_gamma, d_lambda, d_pcg_iters, d_
         rc = lib().mpcgpu_b200_pcg_refstyle_f32(
             ctypes.c_uint32(s), ctypes.c_uint32(N), *args, _ptr(d_ws, f, "d_ws", need // 4), _stream())
     else:
-        rc = lib().mpcgpu_b200_pcg_f32(ctypes.c_uint32(s), ctypes.c_uint32(N),
-                                       ctypes.c_uint32(batch), *args, None, _stream())
+        rc = getattr(lib(), "mpcgpu_b200_pcg_" + sfx)(ctypes.c_uint32(s), ctypes.c_uint32(N),
+                                                      ctypes.c_uint32(batch), *args, None, _stream())
     _check(rc, "pcg")
 
 
@@ -137,14 +148,14 @@ def kkt_solve(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, 
     """Fused form_schur_system + pcg: d_G_dense -> G^-1, d_lambda in/out."""
     s, c, N = state_size, control_size, knot_points
     z = sizes(s, c, N)
-    f = torch.float32
-    rc = lib().mpcgpu_b200_kkt_solve_f32(
+    f, sfx, cT = _prec(d_G_dense, "d_G_dense")
+    rc = getattr(lib(), "mpcgpu_b200_kkt_solve_" + sfx)(
         ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
         _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
         _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
         _ptr(d_g, f, "d_g", z["g"] * batch), _ptr(d_c, f, "d_c", z["c"] * batch),
-        ctypes.c_float(rho), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
-        ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+        cT(rho), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
+        ctypes.c_uint32(config.pcg_max_iter), cT(config.pcg_exit_tol),
         _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", batch),
         _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", batch), None, _stream())
     _check(rc, "kkt_solve")
@@ -155,15 +166,15 @@ def kkt_solve_dz(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_
     """kkt_solve with compute_dz (include/common/dz.cuh:124-133) as the kernel's epilogue."""
     s, c, N = state_size, control_size, knot_points
     z = sizes(s, c, N)
-    f = torch.float32
-    rc = lib().mpcgpu_b200_kkt_solve_dz_f32(
+    f, sfx, cT = _prec(d_G_dense, "d_G_dense")
+    rc = getattr(lib(), "mpcgpu_b200_kkt_solve_dz_" + sfx)(
         ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
         _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
         _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,
         _ptr(d_g, f, "d_g", z["g"] * batch), _ptr(d_c, f, "d_c", z["c"] * batch),
-        ctypes.c_float(rho), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
+        cT(rho), _ptr(d_lambda, f, "d_lambda", z["lambda"] * batch),
         _ptr(d_dz, f, "d_dz", z["g"] * batch),
-        ctypes.c_uint32(config.pcg_max_iter), ctypes.c_float(config.pcg_exit_tol),
+        ctypes.c_uint32(config.pcg_max_iter), cT(config.pcg_exit_tol),
         _ptr(d_pcg_iters, torch.int32, "d_pcg_iters", batch),
         _ptr(d_pcg_exit, d_pcg_exit.dtype, "d_pcg_exit", batch), None, _stream())
     _check(rc, "kkt_solve_dz")
@@ -173,8 +184,8 @@ def compute_dz(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g_
     """compute_dz of include/common/dz.cuh:124-133 (same argument order): d_G_dense holds G^-1."""
     s, c, N = state_size, control_size, knot_points
     z = sizes(s, c, N)
-    f = torch.float32
-    rc = lib().mpcgpu_b200_dz_f32(
+    f, sfx, cT = _prec(d_G_dense, "d_G_dense")
+    rc = getattr(lib(), "mpcgpu_b200_dz_" + sfx)(
         ctypes.c_uint32(s), ctypes.c_uint32(c), ctypes.c_uint32(N), ctypes.c_uint32(batch),
         _ptr(d_G_dense, f, "d_G_dense", z["G"] * batch),
         _ptr(d_C_dense, f, "d_C_dense", z["C"] * batch) if N > 1 else None,

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <string>
 
+#include "capi_internal.h"
 #include "kernels.cuh"
 #include "refstyle_pcg.cuh"
 
@@ -27,6 +28,13 @@ int bad(const char* what) {
     g_err = what;
     return (int)cudaErrorInvalidValue;
 }
+}  // namespace
+namespace mpcb200 { namespace detail {
+int fail(cudaError_t e, const char* what) { return ::fail(e, what); }
+int bad(const char* what) { return ::bad(what); }
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+} }
+namespace {
 
 enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2 };
 

@@ -1,0 +1,160 @@
+// capi_f64.cu -- fp64 twins of the C ABI (include/mpcgpu_b200.h), for builds of the reference with
+// USE_DOUBLES 1 (linsys_t = double, include/common/settings.cuh:49-57).
+// The kernels are the templates of kkt_device.cuh / kernels.cuh instantiated for double:
+//   Cfg<16, CL, 16, 0, double>: 16 knots per 256-thread CTA, ONE row per lane (16 lanes per knot, 14
+//   used), S rows (84 registers) stay in registers, Pinv rows in shared memory (no tensor memory: its
+//   columns are 32 bit and the rows would not fit beside a second copy), pair-wise DFMA, the same
+//   st.async + mbarrier cluster reductions carrying 8-byte partials.  N <= 256 (cluster of 16).
+#include "../../include/mpcgpu_b200.h"
+
+#include <algorithm>
+#include <cstring>
+
+#include "capi_internal.h"
+#include "kernels.cuh"
+
+using namespace mpcb200;
+using detail::bad;
+using detail::fail;
+
+namespace {
+
+using Args = BatchArgsT<double>;
+enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2 };
+
+template <class CF, int KIND>
+cudaError_t launch(const Args& a, cudaStream_t st) {
+    auto kern = (KIND == K_SCHUR) ? schur_kernel<CF> : (KIND == K_PCG) ? pcg_kernel<CF> : fused_kernel<CF>;
+    static thread_local int configured_dev = -1;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (configured_dev != dev) {
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        if (CF::CL > 8) {
+            e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+            if (e != cudaSuccess) return e;
+        }
+        configured_dev = dev;
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)a.batch * CF::CL, 1, 1);
+    cfg.blockDim = dim3(CF::NT, 1, 1);
+    cfg.dynamicSmemBytes = CF::SMEM_BYTES;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CF::CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    e = cudaLaunchKernelEx(&cfg, kern, a);
+    if (e == cudaSuccess) detail::count_launch();
+    return e;
+}
+
+template <int CL> using D = Cfg<16, CL, 16, 0, double>;
+
+template <int KIND>
+cudaError_t dispatch(const Args& a, cudaStream_t st) {
+    const int N = a.N;
+    if (N <= 16) return launch<D<1>, KIND>(a, st);
+    if (N <= 32) return launch<D<2>, KIND>(a, st);
+    if (N <= 64) return launch<D<4>, KIND>(a, st);
+    if (N <= 128) return launch<D<8>, KIND>(a, st);
+    if (N <= 256) return launch<D<16>, KIND>(a, st);
+    return cudaErrorInvalidValue;
+}
+
+Args make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
+    Args a;
+    memset(&a, 0, sizeof(a));
+    a.N = (int)N;
+    a.batch = (int)batch;
+    a.sG = (size_t)(s * s + c * c) * N - c * c;
+    a.sC = (size_t)(s * s + s * c) * (N - 1);
+    a.sg = (size_t)(s + c) * N - c;
+    a.sc = (size_t)s * N;
+    a.sS = (size_t)3 * s * s * N;
+    a.sv = (size_t)s * N;
+    return a;
+}
+
+bool sizes_ok(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
+    return s == 14 && c == 7 && N >= 1 && N <= 256 && batch >= 1 && batch <= (1u << 24);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mpcgpu_b200_schur_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, double* d_G,
+                          const double* d_C, const double* d_g, const double* d_c, double rho,
+                          double* d_S, double* d_Pinv, double* d_gamma, void* stream) {
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_schur_f64: unsupported sizes (need s=14,c=7,1<=N<=256)");
+    if (!d_G || (N > 1 && !d_C) || !d_g || !d_c || !d_S || !d_Pinv || !d_gamma) return bad("mpcgpu_b200_schur_f64: null pointer");
+    Args a = make_args(s, c, N, batch);
+    a.G = d_G; a.C = d_C; a.g = d_g; a.c = d_c; a.rho = rho;
+    a.S = d_S; a.Pinv = d_Pinv; a.gamma = d_gamma;
+    cudaError_t e = dispatch<K_SCHUR>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_schur_f64");
+}
+
+int mpcgpu_b200_pcg_f64(uint32_t s, uint32_t N, uint32_t batch, const double* d_S, const double* d_Pinv,
+                        const double* d_gamma, double* d_lambda, uint32_t max_iter, double exit_tol,
+                        uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws, void* stream) {
+    (void)d_ws;
+    if (!sizes_ok(s, 7, N, batch)) return bad("mpcgpu_b200_pcg_f64: unsupported sizes (need s=14,1<=N<=256)");
+    if (!d_S || !d_Pinv || !d_gamma || !d_lambda || !d_iters || !d_max_iter_exit) return bad("mpcgpu_b200_pcg_f64: null pointer");
+    Args a = make_args(s, 7, N, batch);
+    a.S = const_cast<double*>(d_S); a.Pinv = const_cast<double*>(d_Pinv); a.gamma = const_cast<double*>(d_gamma);
+    a.lambda = d_lambda; a.max_iter = max_iter; a.exit_tol = exit_tol;
+    a.iters = d_iters; a.exits = d_max_iter_exit;
+    cudaError_t e = dispatch<K_PCG>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_pcg_f64");
+}
+
+int mpcgpu_b200_kkt_solve_dz_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, double* d_G,
+                                 const double* d_C, const double* d_g, const double* d_c, double rho,
+                                 double* d_lambda, double* d_dz, uint32_t max_iter, double exit_tol,
+                                 uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws, void* stream) {
+    (void)d_ws;
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_kkt_solve_f64: unsupported sizes (need s=14,c=7,1<=N<=256)");
+    if (!d_G || (N > 1 && !d_C) || !d_g || !d_c || !d_lambda || !d_iters || !d_max_iter_exit) return bad("mpcgpu_b200_kkt_solve_f64: null pointer");
+    Args a = make_args(s, c, N, batch);
+    a.G = d_G; a.C = d_C; a.g = d_g; a.c = d_c; a.rho = rho;
+    a.lambda = d_lambda; a.max_iter = max_iter; a.exit_tol = exit_tol;
+    a.iters = d_iters; a.exits = d_max_iter_exit;
+    a.dz = d_dz; a.sdz = a.sg;
+    cudaError_t e = dispatch<K_FUSED>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_kkt_solve_f64");
+}
+
+int mpcgpu_b200_kkt_solve_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, double* d_G,
+                              const double* d_C, const double* d_g, const double* d_c, double rho,
+                              double* d_lambda, uint32_t max_iter, double exit_tol, uint32_t* d_iters,
+                              uint8_t* d_max_iter_exit, void* d_ws, void* stream) {
+    return mpcgpu_b200_kkt_solve_dz_f64(s, c, N, batch, d_G, d_C, d_g, d_c, rho, d_lambda, nullptr, max_iter,
+                                        exit_tol, d_iters, d_max_iter_exit, d_ws, stream);
+}
+
+int mpcgpu_b200_dz_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, const double* d_Ginv,
+                       const double* d_C, const double* d_g, const double* d_lambda, double* d_dz, void* stream) {
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_dz_f64: unsupported sizes (need s=14,c=7,1<=N<=256)");
+    if (!d_Ginv || (N > 1 && !d_C) || !d_g || !d_lambda || !d_dz) return bad("mpcgpu_b200_dz_f64: null pointer");
+    Args a = make_args(s, c, N, batch);
+    a.G = const_cast<double*>(d_Ginv); a.C = d_C; a.g = d_g; a.lambda = const_cast<double*>(d_lambda);
+    a.dz = d_dz; a.sdz = a.sg;
+    const size_t knots = (size_t)batch * N;
+    const unsigned grid = (unsigned)std::min<size_t>((knots + 31) / 32, 148u * 64u);
+    dz_kernel<double><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(e, "mpcgpu_b200_dz_f64");
+    detail::count_launch();
+    return 0;
+}
+
+}  // extern "C"

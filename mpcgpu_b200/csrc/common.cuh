@@ -74,6 +74,13 @@ __device__ __forceinline__ void st_async_f32(uint32_t cluster_addr, float v, uin
                  "r"(__float_as_uint(v)), "r"(cluster_mbar) : "memory");
 }
 
+__device__ __forceinline__ void st_async_f64(uint32_t cluster_addr, double v, uint32_t cluster_mbar) {
+    asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(cluster_addr),
+                 "l"(__double_as_longlong(v)), "r"(cluster_mbar) : "memory");
+}
+__device__ __forceinline__ void st_async(uint32_t a, float v, uint32_t mb) { st_async_f32(a, v, mb); }
+__device__ __forceinline__ void st_async(uint32_t a, double v, uint32_t mb) { st_async_f64(a, v, mb); }
+
 // ---- tensor memory (TMEM, 128 lanes x 512 columns x 32 bit per SM) as an operand store ----------
 // tcgen05.ld/st .32x32b: warp w of the CTA addresses lanes 32*(w%4)..+31, thread = lane, xN = N
 // consecutive 32-bit columns of that lane.  Measured on B200 (tools/tmem_bw.cu): >= 300 B/clk/SM,
@@ -143,6 +150,12 @@ template <> struct TmemChunk<4> {
 };
 
 __device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;

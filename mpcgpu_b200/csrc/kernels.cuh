@@ -9,20 +9,22 @@
 
 namespace mpcb200 {
 
-struct BatchArgs {
+template <class T>
+struct BatchArgsT {
     int N;
     int batch;
     // per-instance element strides
     size_t sG, sC, sg, sc, sS, sv;
-    float* G; const float* C; const float* g; const float* c;
-    float rho;
-    float* S; float* Pinv; float* gamma;   // two-stage outputs / inputs
-    float* lambda;
-    unsigned max_iter; float exit_tol;
+    T* G; const T* C; const T* g; const T* c;
+    T rho;
+    T* S; T* Pinv; T* gamma;   // two-stage outputs / inputs
+    T* lambda;
+    unsigned max_iter; T exit_tol;
     unsigned* iters; uint8_t* exits;
-    float* dz = nullptr; size_t sdz = 0;   // optional compute_dz epilogue (fused) / output of dz_kernel
-    const float* rho_dev = nullptr;        // optional: rho read from device memory (launches replayed from a CUDA graph)
+    T* dz = nullptr; size_t sdz = 0;   // optional compute_dz epilogue (fused) / output of dz_kernel
+    const T* rho_dev = nullptr;        // optional: rho read from device memory (launches replayed from a CUDA graph)
 };
+using BatchArgs = BatchArgsT<float>;
 
 // PROW column offset of block column `blk` (0 left, 1 diag, 2 right) of the reference layout
 template <class CF>
@@ -32,15 +34,16 @@ __device__ __forceinline__ int prow_col(int blk) { return blk == 1 ? CF::cD : (b
 // include/pcg/linsys_setup_no_precond.cuh:29-38); corner blocks are written as zeros.
 // S rows come from registers, Pinv rows from shared memory (coalesced).
 template <class CF>
-__device__ __forceinline__ void store_rows(const float* smem, const Rows<CF::RPT>& R, float* Sg,
-                                           float* Pg, float* gam, int N) {
+__device__ __forceinline__ void store_rows(const typename CF::T* smem, const RowsOf<CF>& R, typename CF::T* Sg,
+                                           typename CF::T* Pg, typename CF::T* gam, int N) {
+    using T = typename CF::T;
     constexpr int S = 14, SS = S * S;
     const int g = threadIdx.x / CF::LPK, t = threadIdx.x % CF::LPK;
     const int k0 = cluster_rank<CF::CL>() * CF::KPC;
     const int k = k0 + g;
     const RowMap<CF::LPK, CF::RPT, 14> rm(t);
     if (k < N) {
-        float* s0 = Sg + (size_t)k * 3 * SS;
+        T* s0 = Sg + (size_t)k * 3 * SS;
 #pragma unroll
         for (int j = 0; j < CF::RPT; j++) {
             if (!rm.ok[j]) continue;
@@ -65,10 +68,12 @@ __device__ __forceinline__ void store_rows(const float* smem, const Rows<CF::RPT
 // load from the reference layout (load_block_bd semantics); the never-written corner blocks
 // S[0][0], S[N-1][2], Pinv[0][0], Pinv[N-1][2] are NOT read.
 template <class CF>
-__device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const float* __restrict__ Sg,
-                                          const float* __restrict__ Pg,
-                                          const float* __restrict__ gam, int N,
+__device__ __forceinline__ void load_rows(typename CF::T* smem, RowsOf<CF>& R, const typename CF::T* __restrict__ Sg,
+                                          const typename CF::T* __restrict__ Pg,
+                                          const typename CF::T* __restrict__ gam, int N,
                                           bool glob_l = false, bool glob_r = false) {
+    using T = typename CF::T;
+    using T2 = typename CF::T2;
     // glob_l / glob_r: this cluster's first / last knot has a neighbour on ANOTHER rank (knot-range
     // split), so its left / right blocks are real data, not the never-written corner blocks
     constexpr int S = 14, SS = S * S;
@@ -76,7 +81,7 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
     const int k0 = cluster_rank<CF::CL>() * CF::KPC;
     const int k = k0 + g;
     const RowMap<CF::LPK, CF::RPT, 14> rm(t);
-    const float* s0 = Sg + (size_t)k * 3 * SS;
+    const T* s0 = Sg + (size_t)k * 3 * SS;
 #pragma unroll
     for (int j = 0; j < CF::RPT; j++) {
         const bool on = (k < N) && rm.ok[j];
@@ -84,18 +89,18 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
         const int r = rm.row[j];
 #pragma unroll
         for (int c = 0; c < S; c++) {
-            setp(R.Sl[j], c, hl ? __ldg(s0 + 0 * SS + c * S + r) : 0.f);
-            setp(R.Sd[j], c, on ? __ldg(s0 + 1 * SS + c * S + r) : 0.f);
-            setp(R.Sr[j], c, hr ? __ldg(s0 + 2 * SS + c * S + r) : 0.f);
+            setp(R.Sl[j], c, hl ? __ldg(s0 + 0 * SS + c * S + r) : T(0));
+            setp(R.Sd[j], c, on ? __ldg(s0 + 1 * SS + c * S + r) : T(0));
+            setp(R.Sr[j], c, hr ? __ldg(s0 + 2 * SS + c * S + r) : T(0));
         }
-        R.gamma[j] = on ? __ldg(gam + (size_t)k * S + r) : 0.f;
+        R.gamma[j] = on ? __ldg(gam + (size_t)k * S + r) : T(0);
     }
     {
         constexpr int TOT2 = CF::KPC * 3 * SS / 2, ITERS = (TOT2 + CF::NT - 1) / CF::NT;
-        const float2* src = reinterpret_cast<const float2*>(Pg + (size_t)k0 * 3 * SS);
+        const T2* src = reinterpret_cast<const T2*>(Pg + (size_t)k0 * 3 * SS);
         constexpr int UN = 8;     // loads first, stores after: UN loads in flight per lane
         for (int it0 = 0; it0 < ITERS; it0 += UN) {
-            float2 v[UN];
+            T2 v[UN];
 #pragma unroll
             for (int u = 0; u < UN; u++) {
                 const int e2 = threadIdx.x + (it0 + u) * CF::NT;
@@ -103,7 +108,7 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
                 const int gg = e / (3 * SS), blk = (e - gg * 3 * SS) / SS;
                 const int kk = k0 + gg;
                 const bool corner = (kk == 0 && blk == 0 && !glob_l) || (kk == N - 1 && blk == 2 && !glob_r);
-                v[u] = make_float2(0.f, 0.f);
+                v[u] = f2(T(0), T(0));
                 if (it0 + u < ITERS && e2 < TOT2 && kk < N && !corner) v[u] = __ldg(src + e2);
             }
 #pragma unroll
@@ -113,7 +118,7 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
                     const int e = 2 * e2;
                     const int gg = e / (3 * SS), w = e - gg * 3 * SS;
                     const int blk = w / SS, x = w - blk * SS, j = x / S, i = x - j * S;
-                    float* d = smem + CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j;
+                    T* d = smem + CF::oP + (gg + 1) * CF::PK + i * CF::PR + prow_col<CF>(blk) + j;
                     d[0] = v[u].x; d[CF::PR] = v[u].y;
                 }
             }
@@ -121,41 +126,44 @@ __device__ __forceinline__ void load_rows(float* smem, Rows<CF::RPT>& R, const f
     }
     for (int e = threadIdx.x; e < CF::KPC * S; e += CF::NT) {      // row padding (never used in sums)
         const int gg = e / S, i = e - gg * S;
-        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + 42] = 0.f;
-        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + 43] = 0.f;
+        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + 42] = T(0);
+        smem[CF::oP + (gg + 1) * CF::PK + i * CF::PR + 43] = T(0);
     }
     __syncthreads();
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) schur_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) schur_kernel(BatchArgsT<typename CF::T> a) {
     extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
+    using T = typename CF::T;
+    T* smem = reinterpret_cast<T*>(smem4);
     const int b = blockIdx.x / CF::CL;
-    KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
-    Rows<CF::RPT> R;
+    KktPtrs<T> P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
+    RowsOf<CF> R;
     schur_rows<CF>(smem, P, a.N, a.rho, R);
     store_rows<CF>(smem, R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_kernel(BatchArgsT<typename CF::T> a) {
     extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
+    using T = typename CF::T;
+    T* smem = reinterpret_cast<T*>(smem4);
     const int b = blockIdx.x / CF::CL;
-    Rows<CF::RPT> R;
+    RowsOf<CF> R;
     load_rows<CF>(smem, R, a.S + b * a.sS, a.Pinv + b * a.sS, a.gamma + b * a.sv, a.N);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
 }
 
 template <class CF>
-__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a) {
+__global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgsT<typename CF::T> a) {
     extern __shared__ float4 smem4[];
-    float* smem = reinterpret_cast<float*>(smem4);
+    using T = typename CF::T;
+    T* smem = reinterpret_cast<T*>(smem4);
     const int b = blockIdx.x / CF::CL;
-    KktPtrs P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
-    Rows<CF::RPT> R;
+    KktPtrs<T> P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
+    RowsOf<CF> R;
     schur_rows<CF>(smem, P, a.N, a.rho_dev ? __ldg(a.rho_dev) : a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
@@ -166,7 +174,8 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgs a
 }
 
 // compute_dz alone (include/common/dz.cuh:124-133): 32 knots per 256-thread CTA over the whole batch
-__global__ void __launch_bounds__(256) dz_kernel(BatchArgs a) {
+template <class T>
+__global__ void __launch_bounds__(256) dz_kernel(BatchArgsT<T> a) {
     const int t = threadIdx.x & 7, lane = threadIdx.x & 31, base = lane & ~7;
     const unsigned mask = 0xFFu << base;
     const size_t total = (size_t)a.batch * a.N;
@@ -197,7 +206,7 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_split_kernel(SplitAr
     const int c = blockIdx.x / CF::CL;                  // local rank index within this launch
     SplitCtx X{a.grank_first + (unsigned)c, a.world, a.epoch, a.mail};
     const size_t ks = (size_t)c * a.n_local;
-    Rows<CF::RPT> R;
+    RowsOf<CF> R;
     load_rows<CF>(smem, R, a.S + ks * 3 * 196, a.Pinv + ks * 3 * 196, a.gamma + ks * 14, a.n_local,
                   X.grank > 0, X.grank + 1 < X.world);
     pcg_rows<CF, true>(smem, R, a.lambda + ks * 14, a.n_local, a.max_iter, a.exit_tol, a.iters + c,

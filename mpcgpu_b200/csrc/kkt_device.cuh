@@ -36,10 +36,19 @@ namespace mpcb200 {
 #endif
 constexpr int pow2_at_least(int x) { int p = 32; while (p < x) p *= 2; return p; }
 
-// TM_ = 1: the PCG phase keeps the Pinv rows in tensor memory instead of shared memory
-template <int KPC_, int CL_, int LPK_, int TM_ = MPCB200_PINV_TMEM>
+// scalar traits: T2 = the 16 B (double) / 8 B (float) pair type all pair-wise arithmetic runs on
+template <class T> struct Num;
+template <> struct Num<float>  { using T2 = float2; };
+template <> struct Num<double> { using T2 = double2; };
+
+// TM_ = 1: the PCG phase keeps the Pinv rows in tensor memory instead of shared memory (fp32 only)
+// T_: float (settings.cuh USE_DOUBLES 0, the reference default) or double (USE_DOUBLES 1)
+template <int KPC_, int CL_, int LPK_, int TM_ = MPCB200_PINV_TMEM, class T_ = float>
 struct Cfg {
-    static constexpr bool TM = TM_ != 0;
+    using T = T_;
+    using T2 = typename Num<T_>::T2;
+    static constexpr bool F32 = sizeof(T_) == 4;
+    static constexpr bool TM = TM_ != 0 && F32;
     static constexpr int S = 14, C = 7;
     static constexpr int KPC = KPC_, CL = CL_;
     static constexpr int LPK = LPK_;            // lanes per knot
@@ -73,36 +82,48 @@ struct Cfg {
     static constexpr int TPT = TNCH * TCH;              // columns per thread
     static constexpr int TCOLS = pow2_at_least(((NW + 3) / 4) * TPT);   // allocation, power of two <= 512
     static_assert(!TM || TCOLS <= 512, "tensor memory has 512 columns");
-    static constexpr size_t SMEM_BYTES = sizeof(float) * FLOATS;
-    static constexpr int MIN_CTAS = (LPK == 4) ? (256 / NT > 0 ? 256 / NT : 1) : (512 / NT > 0 ? 512 / NT : 1);
-    static_assert(LPK == 4 || LPK == 8, "4 or 8 lanes per knot");
+    static constexpr size_t SMEM_BYTES = sizeof(T) * FLOATS;
+    static constexpr int MIN_CTAS = !F32 ? 1 : (LPK == 4) ? (256 / NT > 0 ? 256 / NT : 1) : (512 / NT > 0 ? 512 / NT : 1);
+    static_assert(LPK == 4 || LPK == 8 || LPK == 16, "4, 8 or 16 lanes per knot");
     static_assert(NT % 32 == 0 && NT <= 1024, "whole warps, <= 1024 threads");
     static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory of sm_100");
 };
 
 // Per-instance views of the reference buffers (include/pcg/sqp.cuh:54-58).
+template <class T>
 struct KktPtrs {
-    float* G;         // in: [Q_k | R_k]; out: [Qt_k^-1 | Rt_k^-1]
-    const float* C;   // [Abar_k | Bbar_k]
-    const float* g;   // [q_k | r_k]
-    const float* c;   // constraint residuals
+    T* G;         // in: [Q_k | R_k]; out: [Qt_k^-1 | Rt_k^-1]
+    const T* C;   // [Abar_k | Bbar_k]
+    const T* g;   // [q_k | r_k]
+    const T* c;   // constraint residuals
 };
 
 // Register-resident part of a knot's block rows: the lane's RPT rows of the stored (negated)
-// Schur complement, as float2 pairs.
-template <int RPT>
+// Schur complement, as pairs.
+template <class T, int RPT>
 struct Rows {
-    float2 Sl[RPT][7], Sd[RPT][7], Sr[RPT][7];
-    float gamma[RPT];
+    typename Num<T>::T2 Sl[RPT][7], Sd[RPT][7], Sr[RPT][7];
+    T gamma[RPT];
 };
+template <class CF> using RowsOf = Rows<typename CF::T, CF::RPT>;
 
-// ---- small float2 helpers ----------------------------------------------------------------
+// ---- small pair helpers (float2: FFMA2; double2: two DFMAs) ---------------------------------
 __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b); }
 __device__ __forceinline__ float2 splat(float a) { return make_float2(a, a); }
 __device__ __forceinline__ float2 neg2(float2 a) { return make_float2(-a.x, -a.y); }
 __device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ double2 f2(double a, double b) { return make_double2(a, b); }
+__device__ __forceinline__ double2 splat(double a) { return make_double2(a, a); }
+__device__ __forceinline__ double2 neg2(double2 a) { return make_double2(-a.x, -a.y); }
+__device__ __forceinline__ double2 fma2(double2 a, double2 b, double2 c) { return make_double2(fma(a.x, b.x, c.x), fma(a.y, b.y, c.y)); }
+__device__ __forceinline__ float fm(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double fm(double a, double b, double c) { return fma(a, b, c); }
+__device__ __forceinline__ float absT(float a) { return fabsf(a); }
+__device__ __forceinline__ double absT(double a) { return fabs(a); }
 __device__ __forceinline__ float getp(const float2 (&a)[7], int i) { return (i & 1) ? a[i >> 1].y : a[i >> 1].x; }
 __device__ __forceinline__ void setp(float2 (&a)[7], int i, float v) { if (i & 1) a[i >> 1].y = v; else a[i >> 1].x = v; }
+__device__ __forceinline__ double getp(const double2 (&a)[7], int i) { return (i & 1) ? a[i >> 1].y : a[i >> 1].x; }
+__device__ __forceinline__ void setp(double2 (&a)[7], int i, double v) { if (i & 1) a[i >> 1].y = v; else a[i >> 1].x = v; }
 
 // 14 floats from a 16 B aligned address (reads 16 floats; the last two are ignored)
 __device__ __forceinline__ void ld14_v4(float2 (&r)[7], const float* p) {
@@ -130,21 +151,53 @@ __device__ __forceinline__ void st14_v2(float* p, const float2 (&r)[7]) {
 #pragma unroll
     for (int q = 0; q < 7; q++) d[q] = r[q];
 }
+// doubles: every 14-element run starts at an even element offset, i.e. 16 B aligned -> seven 16 B accesses
+__device__ __forceinline__ void ld14_v2(double2 (&r)[7], const double* p) {
+    const double2* s = reinterpret_cast<const double2*>(p);
+#pragma unroll
+    for (int q = 0; q < 7; q++) r[q] = s[q];
+}
+__device__ __forceinline__ void ld14_v4(double2 (&r)[7], const double* p) { ld14_v2(r, p); }
+__device__ __forceinline__ void st14_v2(double* p, const double2 (&r)[7]) {
+    double2* d = reinterpret_cast<double2*>(p);
+#pragma unroll
+    for (int q = 0; q < 7; q++) d[q] = r[q];
+}
+__device__ __forceinline__ void st14_v4(double* p, const double2 (&r)[7]) { st14_v2(p, r); }
+// 8 elements (a 7-row padded to 8) to / from a 16 B aligned address
+__device__ __forceinline__ void st8(float* p, const float (&a)[8]) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(a[0], a[1], a[2], a[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(a[4], a[5], a[6], a[7]);
+}
+__device__ __forceinline__ void ld8(float (&a)[8], const float* p) {
+    const float4 u = reinterpret_cast<const float4*>(p)[0], v = reinterpret_cast<const float4*>(p)[1];
+    a[0] = u.x; a[1] = u.y; a[2] = u.z; a[3] = u.w; a[4] = v.x; a[5] = v.y; a[6] = v.z; a[7] = v.w;
+}
+__device__ __forceinline__ void st8(double* p, const double (&a)[8]) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) reinterpret_cast<double2*>(p)[q] = make_double2(a[2 * q], a[2 * q + 1]);
+}
+__device__ __forceinline__ void ld8(double (&a)[8], const double* p) {
+#pragma unroll
+    for (int q = 0; q < 4; q++) { const double2 v = reinterpret_cast<const double2*>(p)[q]; a[2 * q] = v.x; a[2 * q + 1] = v.y; }
+}
 
-// dot of a 14-row (float2 pairs) with 14 floats: two interleaved partial sums (even / odd)
-__device__ __forceinline__ float2 dot14_acc(const float2 (&a)[7], const float2 (&x)[7], float2 acc) {
+// dot of a 14-row (pairs) with 14 values: two interleaved partial sums (even / odd)
+template <class T2>
+__device__ __forceinline__ T2 dot14_acc(const T2 (&a)[7], const T2 (&x)[7], T2 acc) {
 #pragma unroll
     for (int q = 0; q < 7; q++) acc = fma2(a[q], x[q], acc);
     return acc;
 }
 __device__ __forceinline__ float hsum(float2 a) { return a.x + a.y; }
+__device__ __forceinline__ double hsum(double2 a) { return a.x + a.y; }
 
 // c[j] += a[j] * b for the lane's RPT rows (one broadcast row b shared by all of them)
-template <int RPT>
-__device__ __forceinline__ void axpy_rows(float2 (&c)[RPT][7], const float (&a)[RPT], const float2 (&b)[7]) {
+template <int RPT, class T, class T2>
+__device__ __forceinline__ void axpy_rows(T2 (&c)[RPT][7], const T (&a)[RPT], const T2 (&b)[7]) {
 #pragma unroll
     for (int j = 0; j < RPT; j++) {
-        const float2 s = splat(a[j]);
+        const T2 s = splat(a[j]);
 #pragma unroll
         for (int q = 0; q < 7; q++) c[j][q] = fma2(s, b[q], c[j][q]);
     }
@@ -167,26 +220,26 @@ struct RowMap {
 // owns rows t + LPK*j).  Same elimination sequence as the reference's invertMatrix on [A | I]
 // (include/utils/matrix.cuh:120-238): the in-place form keeps the evolving inverse column in
 // the slot of the eliminated one.  `piv`: 16 floats of shared memory private to this knot.
-template <int LPK, int RPT>
-__device__ __forceinline__ void gj14(float2 (&a)[RPT][7], int t, float* piv) {
+template <int LPK, int RPT, class T2, class T>
+__device__ __forceinline__ void gj14(T2 (&a)[RPT][7], int t, T* piv) {
 #pragma unroll
     for (int p = 0; p < 14; p++) {
         const int owner = p % LPK, slot = p / LPK;
         if (t == owner) st14_v4(piv, a[slot]);
         __syncwarp();
-        float2 rp[7];
+        T2 rp[7];
         ld14_v4(rp, piv);
         __syncwarp();
-        const float pinv = 1.0f / getp(rp, p);
+        const T pinv = T(1) / getp(rp, p);
 #pragma unroll
         for (int j = 0; j < RPT; j++) {
-            const float f = getp(a[j], p) * pinv;
+            const T f = getp(a[j], p) * pinv;
             if (j == slot && t == owner) {
 #pragma unroll
                 for (int q = 0; q < 7; q++) a[j][q] = f2(rp[q].x * pinv, rp[q].y * pinv);
                 setp(a[j], p, pinv);
             } else {
-                const float2 nf = splat(-f);
+                const T2 nf = splat(-f);
 #pragma unroll
                 for (int q = 0; q < 7; q++) a[j][q] = fma2(nf, rp[q], a[j][q]);
                 setp(a[j], p, -f);
@@ -195,24 +248,24 @@ __device__ __forceinline__ void gj14(float2 (&a)[RPT][7], int t, float* piv) {
     }
 }
 
-// 7 x 7 Gauss-Jordan, rows t + LPK*j (8 floats per row, last one padding).  piv: 8 floats.
-template <int LPK, int RPT7>
-__device__ __forceinline__ void gj7(float (&a)[RPT7][8], int t, float* piv) {
+// 7 x 7 Gauss-Jordan, rows t + LPK*j (8 values per row, last one padding).  piv: 8 values.
+template <int LPK, int RPT7, class T>
+__device__ __forceinline__ void gj7(T (&a)[RPT7][8], int t, T* piv) {
 #pragma unroll
     for (int p = 0; p < 7; p++) {
         const int owner = p % LPK, slot = p / LPK;
         if (t == owner) {
-            reinterpret_cast<float4*>(piv)[0] = make_float4(a[slot][0], a[slot][1], a[slot][2], a[slot][3]);
-            reinterpret_cast<float4*>(piv)[1] = make_float4(a[slot][4], a[slot][5], a[slot][6], 0.f);
+            const T row[8] = {a[slot][0], a[slot][1], a[slot][2], a[slot][3], a[slot][4], a[slot][5], a[slot][6], T(0)};
+            st8(piv, row);
         }
         __syncwarp();
-        const float4 u = reinterpret_cast<const float4*>(piv)[0], v = reinterpret_cast<const float4*>(piv)[1];
+        T rp[8];
+        ld8(rp, piv);
         __syncwarp();
-        const float rp[7] = {u.x, u.y, u.z, u.w, v.x, v.y, v.z};
-        const float pinv = 1.0f / rp[p];
+        const T pinv = T(1) / rp[p];
 #pragma unroll
         for (int j = 0; j < RPT7; j++) {
-            const float f = a[j][p] * pinv;
+            const T f = a[j][p] * pinv;
             if (j == slot && t == owner) {
 #pragma unroll
                 for (int c = 0; c < 7; c++) a[j][c] = rp[c] * pinv;
@@ -220,7 +273,7 @@ __device__ __forceinline__ void gj7(float (&a)[RPT7][8], int t, float* piv) {
             } else {
 #pragma unroll
                 for (int c = 0; c < 7; c++)
-                    if (c != p) a[j][c] = fmaf(-f, rp[c], a[j][c]);
+                    if (c != p) a[j][c] = fm(-f, rp[c], a[j][c]);
                 a[j][p] = -f;
             }
         }
@@ -229,19 +282,22 @@ __device__ __forceinline__ void gj7(float (&a)[RPT7][8], int t, float* piv) {
 
 // copy one neighbour-CTA region into local shared memory (cluster kernels only)
 template <class CF>
-__device__ __forceinline__ void pull_floats(float* dst, float* src_local_addr, int n, unsigned src_rank) {
-    const float2* src = reinterpret_cast<const float2*>(map_rank<CF::CL>(src_local_addr, src_rank));
-    float2* d = reinterpret_cast<float2*>(dst);
+__device__ __forceinline__ void pull_floats(typename CF::T* dst, typename CF::T* src_local_addr, int n, unsigned src_rank) {
+    using T2 = typename CF::T2;
+    const T2* src = reinterpret_cast<const T2*>(map_rank<CF::CL>(src_local_addr, src_rank));
+    T2* d = reinterpret_cast<T2*>(dst);
     for (int q = threadIdx.x; q < n / 2; q += CF::NT) d[q] = src[q];
 }
 // Pd columns (14 x 14, row stride PR) of one PROW knot from a neighbour CTA
 template <class CF>
-__device__ __forceinline__ void pull_pd(float* smem, int dst_slot, int src_slot, unsigned src_rank) {
-    const float* src = map_rank<CF::CL>(smem + CF::oP + src_slot * CF::PK, src_rank);
-    float* dst = smem + CF::oP + dst_slot * CF::PK;
+__device__ __forceinline__ void pull_pd(typename CF::T* smem, int dst_slot, int src_slot, unsigned src_rank) {
+    using T = typename CF::T;
+    using T2 = typename CF::T2;
+    const T* src = map_rank<CF::CL>(smem + CF::oP + src_slot * CF::PK, src_rank);
+    T* dst = smem + CF::oP + dst_slot * CF::PK;
     for (int q = threadIdx.x; q < 14 * 7; q += CF::NT) {
         const int row = q / 7, c2 = q - row * 7;
-        reinterpret_cast<float2*>(dst + row * CF::PR)[c2] = reinterpret_cast<const float2*>(src + row * CF::PR)[c2];
+        reinterpret_cast<T2*>(dst + row * CF::PR)[c2] = reinterpret_cast<const T2*>(src + row * CF::PR)[c2];
     }
 }
 
@@ -250,8 +306,10 @@ __device__ __forceinline__ void pull_pd(float* smem, int dst_slot, int src_slot,
 // Leaves S rows and gamma in registers and the Pinv rows in PROW; writes G^-1 in place.
 // ---------------------------------------------------------------------------------------
 template <class CF>
-__device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N, float rho,
-                                           Rows<CF::RPT>& R) {
+__device__ __forceinline__ void schur_rows(typename CF::T* smem, const KktPtrs<typename CF::T>& P, int N,
+                                           typename CF::T rho, RowsOf<CF>& R) {
+    using T = typename CF::T;
+    using T2 = typename CF::T2;
     constexpr int S = 14, C = 7, KPC = CF::KPC, CL = CF::CL, PR = CF::PR, PK = CF::PK, TK = CF::TK;
     constexpr int LPK = CF::LPK, RPT = CF::RPT, RPT7 = CF::RPT7;
     constexpr int SS = S * S, CC = C * C, SC = S * C;
@@ -269,37 +327,37 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     const bool has_right = valid && (k + 1 < N);
     const int sl = g + 1;
 
-    float* PW = smem + CF::oP;                    // PROW
-    float* TA = smem + CF::oT;
-    float* myP = PW + sl * PK;
-    float* myT = TA + sl * TK;
+    T* PW = smem + CF::oP;                    // PROW
+    T* TA = smem + CF::oT;
+    T* myP = PW + sl * PK;
+    T* myT = TA + sl * TK;
     // scratch living in the not-yet-written Pl / Pr columns of this knot's PROW rows
-    float* vq = myP + 0 * PR + cR;                // q_k
-    float* vqm = myP + 1 * PR + cR;               // q_{k-1}
-    float* vc = myP + 2 * PR + cR;                // c_k
-    float* vrm = myP + 3 * PR + cR;               // r_{k-1} (7, padded to 8)
-    float* piv = myP + 4 * PR + cR;               // pivot row broadcast (16 B aligned, + 2 pad)
+    T* vq = myP + 0 * PR + cR;                // q_k
+    T* vqm = myP + 1 * PR + cR;               // q_{k-1}
+    T* vc = myP + 2 * PR + cR;                // c_k
+    T* vrm = myP + 3 * PR + cR;               // r_{k-1} (7, padded to 8)
+    T* piv = myP + 4 * PR + cR;               // pivot row broadcast (16 B aligned, + 2 pad)
     // B_{k-1} column m: myP[m*PR + cL .. +13] (m < 7); Rt^-1 row m: myP[(7+m)*PR + cL .. +7]
 
     // ---- stage [Abar_{k-1} | Bbar_{k-1}] (one contiguous run per knot), coalesced ----------
-    // (float2 granularity: CSET, SS and S are even, so a pair never straddles a column; fixed
+    // (T2 granularity: CSET, SS and S are even, so a pair never straddles a column; fixed
     // trip count + unroll keeps 8 loads in flight per lane instead of one)
     {
         constexpr int TOT2 = KPC * CSET / 2, ITERS = (TOT2 + CF::NT - 1) / CF::NT;
-        const float2* src = reinterpret_cast<const float2*>(P.C + ((ptrdiff_t)k0 - 1) * CSET);
+        const T2* src = reinterpret_cast<const T2*>(P.C + ((ptrdiff_t)k0 - 1) * CSET);
         // loads first (branch-free, UN in flight per lane), stores after: with the store's branches
         // in between the compiler keeps ONE load in flight and the CTA waits out ITERS HBM round trips
-        // latency tilings (<= 20 float2 per lane): the whole tile in flight at once; the 64-knot
+        // latency tilings (<= 20 T2 per lane): the whole tile in flight at once; the 64-knot
         // throughput tiling measured best with 8 (1.23M vs 1.21M solves/s with all 37)
         constexpr int UN = ITERS <= 20 ? ITERS : 8;
         for (int it0 = 0; it0 < ITERS; it0 += UN) {
-            float2 v[UN];
+            T2 v[UN];
 #pragma unroll
             for (int u = 0; u < UN; u++) {
                 const int i2 = tid + (it0 + u) * CF::NT;
                 const int kk = k0 + (2 * i2) / CSET;
                 const bool ld = (it0 + u < ITERS) && i2 < TOT2 && kk >= 1 && kk < N;
-                v[u] = f2(0.f, 0.f);
+                v[u] = f2(T(0), T(0));
                 if (ld) v[u] = __ldg(src + i2);
             }
 #pragma unroll
@@ -308,55 +366,55 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
                 if (it0 + u < ITERS && i2 < TOT2) {
                     const int idx = 2 * i2;
                     const int gg = idx / CSET, e = idx - gg * CSET;
-                    if (e < SS) *reinterpret_cast<float2*>(TA + (gg + 1) * TK + e) = v[u];     // column-major A
+                    if (e < SS) *reinterpret_cast<T2*>(TA + (gg + 1) * TK + e) = v[u];     // column-major A
                     else {
                         const int m = (e - SS) / S, i = (e - SS) - m * S;
-                        *reinterpret_cast<float2*>(PW + (gg + 1) * PK + m * PR + cL + i) = v[u];
+                        *reinterpret_cast<T2*>(PW + (gg + 1) * PK + m * PR + cL + i) = v[u];
                     }
                 }
             }
         }
     }
     // halo knots: keep every tile that an edge knot may read finite
-    for (int q = tid; q < 2 * PK; q += CF::NT) PW[(q < PK) ? q : (KPC + 1) * PK + (q - PK)] = 0.f;
-    for (int q = tid; q < 2 * TK; q += CF::NT) TA[(q < TK) ? q : (KPC + 1) * TK + (q - TK)] = 0.f;
+    for (int q = tid; q < 2 * PK; q += CF::NT) PW[(q < PK) ? q : (KPC + 1) * PK + (q - PK)] = T(0);
+    for (int q = tid; q < 2 * TK; q += CF::NT) TA[(q < TK) ? q : (KPC + 1) * TK + (q - TK)] = T(0);
 
     // ---- loads: Qt_k rows, Rt_{k-1} rows, vectors ------------------------------------------
-    float2 aQ[RPT][7];
+    T2 aQ[RPT][7];
 #pragma unroll
     for (int j = 0; j < RPT; j++) {
 #pragma unroll
         for (int c = 0; c < 14; c++) {
-            float v = 0.f;
+            T v = T(0);
             if (valid && rm.ok[j]) v = P.G[(size_t)k * GSET + c * S + rm.row[j]];
-            setp(aQ[j], c, v + ((c == t + LPK * j) ? rho : 0.f));       // linsys_setup.cuh:180,329-330
+            setp(aQ[j], c, v + ((c == t + LPK * j) ? rho : T(0)));       // linsys_setup.cuh:180,329-330
         }
     }
-    float aR[RPT7][8];
+    T aR[RPT7][8];
 #pragma unroll
     for (int j = 0; j < RPT7; j++) {
 #pragma unroll
         for (int c = 0; c < 7; c++) {
-            float v = 0.f;
+            T v = T(0);
             if (inner && rm7.ok[j]) v = P.G[(size_t)(k - 1) * GSET + SS + c * C + rm7.row[j]];
-            aR[j][c] = v + ((c == t + LPK * j) ? rho : 0.f);            // :331
+            aR[j][c] = v + ((c == t + LPK * j) ? rho : T(0));            // :331
         }
-        aR[j][7] = 0.f;
+        aR[j][7] = T(0);
     }
     __syncthreads();                               // staging done (vectors overwrite zeroed chunks)
 #pragma unroll
     for (int j = 0; j < RPT; j++) {
         if (rm.ok[j]) {
             const int r = rm.row[j];
-            vq[r] = valid ? __ldg(P.g + (size_t)k * gSET + r) : 0.f;
-            vqm[r] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + r) : 0.f;
-            vc[r] = inner ? __ldg(P.c + (size_t)k * S + r) : 0.f;
+            vq[r] = valid ? __ldg(P.g + (size_t)k * gSET + r) : T(0);
+            vqm[r] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + r) : T(0);
+            vc[r] = inner ? __ldg(P.c + (size_t)k * S + r) : T(0);
         }
     }
 #pragma unroll
     for (int j = 0; j < RPT7; j++)
-        if (rm7.ok[j]) vrm[rm7.row[j]] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + S + rm7.row[j]) : 0.f;
-    if (t == 0) vrm[7] = 0.f;
+        if (rm7.ok[j]) vrm[rm7.row[j]] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + S + rm7.row[j]) : T(0);
+    if (t == 0) vrm[7] = T(0);
     // knot 0: Pinv[0][1] = -Qt_0, stored BEFORE inversion (linsys_setup.cuh:202-210); its A
     // tile is unused, park the rows there
     if (k == 0) {
@@ -382,18 +440,18 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
             for (int c = 0; c < 7; c++) P.G[(size_t)(k - 1) * GSET + SS + c * C + rm7.row[j]] = aR[j][c];   // :375
         }
         if (rm7.ok[j]) {
-            float2* rr = reinterpret_cast<float2*>(myP + (7 + rm7.row[j]) * PR + cL);
+            T2* rr = reinterpret_cast<T2*>(myP + (7 + rm7.row[j]) * PR + cL);
             rr[0] = f2(aR[j][0], aR[j][1]); rr[1] = f2(aR[j][2], aR[j][3]);
-            rr[2] = f2(aR[j][4], aR[j][5]); rr[3] = f2(aR[j][6], 0.f);
+            rr[2] = f2(aR[j][4], aR[j][5]); rr[3] = f2(aR[j][6], T(0));
         }
     }
     __syncwarp();
-    float ti[RPT];                                                     // Qt_k^-1 q_k  (:411-415, :260)
+    T ti[RPT];                                                     // Qt_k^-1 q_k  (:411-415, :260)
     {
-        float2 x[7];
+        T2 x[7];
         ld14_v4(x, vq);
 #pragma unroll
-        for (int j = 0; j < RPT; j++) ti[j] = hsum(dot14_acc(aQ[j], x, splat(0.f)));
+        for (int j = 0; j < RPT; j++) ti[j] = hsum(dot14_acc(aQ[j], x, splat(T(0))));
     }
 
     cluster_sync_all<CL>();
@@ -403,71 +461,71 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     }
 
     // ---- phase 1b: phi, theta, gamma, theta^-1 ----------------------------------------------
-    float2 th[RPT][7];
+    T2 th[RPT][7];
     {
-        float2 phi[RPT][7];
+        T2 phi[RPT][7];
 #pragma unroll
         for (int j = 0; j < RPT; j++)
 #pragma unroll
-            for (int q = 0; q < 7; q++) { phi[j][q] = splat(0.f); th[j][q] = aQ[j][q]; }   // + Qt_k^-1 (:466)
-        const float* Qm = PW + (sl - 1) * PK + cD;                     // Qt_{k-1}^-1 rows
+            for (int q = 0; q < 7; q++) { phi[j][q] = splat(T(0)); th[j][q] = aQ[j][q]; }   // + Qt_k^-1 (:466)
+        const T* Qm = PW + (sl - 1) * PK + cD;                     // Qt_{k-1}^-1 rows
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // phi = A Qt_{k-1}^-1   (:398)
-            float2 b[7];
+            T2 b[7];
             ld14_v4(b, Qm + m * PR);
-            float a[RPT];
+            T a[RPT];
 #pragma unroll
             for (int j = 0; j < RPT; j++) a[j] = myT[m * S + rm.row[j]];
             axpy_rows<RPT>(phi, a, b);
         }
-        float br[RPT][7];
+        T br[RPT][7];
 #pragma unroll
         for (int j = 0; j < RPT; j++)
 #pragma unroll
-            for (int c = 0; c < 7; c++) br[j][c] = 0.f;
+            for (int c = 0; c < 7; c++) br[j][c] = T(0);
 #pragma unroll
         for (int m = 0; m < 7; m++) {                                  // BR = B Rt_{k-1}^-1    (:406)
-            const float2* rr = reinterpret_cast<const float2*>(myP + (7 + m) * PR + cL);
-            const float2 u0 = rr[0], u1 = rr[1], u2 = rr[2], u3 = rr[3];
-            const float rmv[7] = {u0.x, u0.y, u1.x, u1.y, u2.x, u2.y, u3.x};
+            const T2* rr = reinterpret_cast<const T2*>(myP + (7 + m) * PR + cL);
+            const T2 u0 = rr[0], u1 = rr[1], u2 = rr[2], u3 = rr[3];
+            const T rmv[7] = {u0.x, u0.y, u1.x, u1.y, u2.x, u2.y, u3.x};
 #pragma unroll
             for (int j = 0; j < RPT; j++) {
-                const float b = myP[m * PR + cL + rm.row[j]];
+                const T b = myP[m * PR + cL + rm.row[j]];
 #pragma unroll
-                for (int c = 0; c < 7; c++) br[j][c] = fmaf(b, rmv[c], br[j][c]);
+                for (int c = 0; c < 7; c++) br[j][c] = fm(b, rmv[c], br[j][c]);
             }
         }
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // + phi A^T             (:447)
-            float2 b[7];
+            T2 b[7];
             ld14_v2(b, myT + m * S);                                   // column m of A
-            float a[RPT];
+            T a[RPT];
 #pragma unroll
             for (int j = 0; j < RPT; j++) a[j] = getp(phi[j], m);
             axpy_rows<RPT>(th, a, b);
         }
 #pragma unroll
         for (int m = 0; m < 7; m++) {                                  // + BR B^T              (:473,:485)
-            float2 b[7];
+            T2 b[7];
             ld14_v2(b, myP + m * PR + cL);                             // column m of B
-            float a[RPT];
+            T a[RPT];
 #pragma unroll
             for (int j = 0; j < RPT; j++) a[j] = br[j][m];
             axpy_rows<RPT>(th, a, b);
         }
         // gamma  (:416-443)
         {
-            float2 x[7];
+            T2 x[7];
             ld14_v4(x, vqm);
-            const float4 ra = reinterpret_cast<const float4*>(vrm)[0], rb = reinterpret_cast<const float4*>(vrm)[1];
-            const float rv[7] = {ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, rb.z};
+            T rv[8];
+            ld8(rv, vrm);
 #pragma unroll
             for (int j = 0; j < RPT; j++) {
-                const float s = hsum(dot14_acc(phi[j], x, splat(0.f)));
-                float d = 0.f;
+                const T s = hsum(dot14_acc(phi[j], x, splat(T(0))));
+                T d = T(0);
 #pragma unroll
-                for (int c = 0; c < 7; c++) d = fmaf(br[j][c], rv[c], d);
-                const float gm = (ti[j] - vc[rm.row[j]]) + (d + s);
+                for (int c = 0; c < 7; c++) d = fm(br[j][c], rv[c], d);
+                const T gm = (ti[j] - vc[rm.row[j]]) + (d + s);
                 R.gamma[j] = inner ? -gm : -ti[j];                     // :531 / :274
             }
         }
@@ -490,7 +548,7 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
     for (int j = 0; j < RPT; j++) {
         if (k == 0) ld14_v2(th[j], myT + rm.row[j] * S);
         if (rm.ok[j]) {
-            float2 n[7];
+            T2 n[7];
 #pragma unroll
             for (int q = 0; q < 7; q++) n[q] = neg2(th[j][q]);
             st14_v4(myP + rm.row[j] * PR + cD, n);
@@ -505,38 +563,38 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
 
     // ---- phase 2: Pinv left block = theta_k^-1 phi_k theta_{k-1}^-1 (stored sign, :97-115) ----
     {
-        float2 t1[RPT][7], pl[RPT][7];
+        T2 t1[RPT][7], pl[RPT][7];
 #pragma unroll
         for (int j = 0; j < RPT; j++)
 #pragma unroll
-            for (int q = 0; q < 7; q++) { t1[j][q] = splat(0.f); pl[j][q] = splat(0.f); }
+            for (int q = 0; q < 7; q++) { t1[j][q] = splat(T(0)); pl[j][q] = splat(T(0)); }
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // theta_k^-1 phi_k        (:100)
-            float2 b[7];
+            T2 b[7];
             ld14_v2(b, myT + m * S);
-            float a[RPT];
+            T a[RPT];
 #pragma unroll
             for (int j = 0; j < RPT; j++) a[j] = getp(th[j], m);
             axpy_rows<RPT>(t1, a, b);
         }
-        const float* Pm = PW + (sl - 1) * PK + cD;                     // -theta_{k-1}^-1 rows
+        const T* Pm = PW + (sl - 1) * PK + cD;                     // -theta_{k-1}^-1 rows
 #pragma unroll
         for (int m = 0; m < 14; m++) {                                 // ... theta_{k-1}^-1      (:102)
-            float2 b[7];
+            T2 b[7];
             ld14_v4(b, Pm + m * PR);
-            float a[RPT];
+            T a[RPT];
 #pragma unroll
             for (int j = 0; j < RPT; j++) a[j] = -getp(t1[j], m);
             axpy_rows<RPT>(pl, a, b);
         }
         // own rows -> Pl columns; transposed -> Pr columns of the left neighbour (:118-136 by symmetry)
-        float* left = PW + (sl - 1) * PK + cR;
+        T* left = PW + (sl - 1) * PK + cR;
         if (CL > 1 && g == 0 && rank > 0) left = map_rank<CL>(PW + KPC * PK + cR, rank - 1);
 #pragma unroll
         for (int j = 0; j < RPT; j++) {
             if (!inner) {
 #pragma unroll
-                for (int q = 0; q < 7; q++) pl[j][q] = splat(0.f);
+                for (int q = 0; q < 7; q++) pl[j][q] = splat(T(0));
             }
             if (rm.ok[j]) {
                 st14_v2(myP + rm.row[j] * PR + cL, pl[j]);
@@ -551,25 +609,25 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
         for (int j = 0; j < RPT; j++)
             if (rm.ok[j]) {
 #pragma unroll
-                for (int c = 0; c < 14; c++) myP[c * PR + cR + rm.row[j]] = 0.f;
+                for (int c = 0; c < 14; c++) myP[c * PR + cR + rm.row[j]] = T(0);
             }
     }
     // ---- S left rows (own phi rows) and right rows (-phi_{k+1}^T, :537-557) ------------------
     {
-        const float* phin = TA + (sl + 1) * TK;
+        const T* phin = TA + (sl + 1) * TK;
 #pragma unroll
         for (int j = 0; j < RPT; j++) {
-            float2 a[7];
+            T2 a[7];
             ld14_v2(a, myT + rm.row[j] * S);
             const bool on = valid && rm.ok[j];
 #pragma unroll
-            for (int q = 0; q < 7; q++) R.Sl[j][q] = (inner && rm.ok[j]) ? neg2(a[q]) : splat(0.f);
+            for (int q = 0; q < 7; q++) R.Sl[j][q] = (inner && rm.ok[j]) ? neg2(a[q]) : splat(T(0));
 #pragma unroll
-            for (int c = 0; c < 14; c++) setp(R.Sr[j], c, (has_right && rm.ok[j]) ? -phin[c * S + rm.row[j]] : 0.f);
+            for (int c = 0; c < 14; c++) setp(R.Sr[j], c, (has_right && rm.ok[j]) ? -phin[c * S + rm.row[j]] : T(0));
             if (!on) {
 #pragma unroll
-                for (int q = 0; q < 7; q++) R.Sd[j][q] = splat(0.f);
-                R.gamma[j] = 0.f;
+                for (int q = 0; q < 7; q++) R.Sd[j][q] = splat(T(0));
+                R.gamma[j] = T(0);
             }
         }
     }
@@ -579,7 +637,7 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
         for (int j = 0; j < RPT; j++)
             if (rm.ok[j]) {
 #pragma unroll
-                for (int q = 0; q < 11; q++) reinterpret_cast<float4*>(myP + rm.row[j] * PR)[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int q = 0; q < PR / 2; q++) reinterpret_cast<T2*>(myP + rm.row[j] * PR)[q] = splat(T(0));
             }
     }
 }
@@ -594,52 +652,68 @@ __device__ __forceinline__ void schur_rows(float* smem, const KktPtrs& P, int N,
 //           All lanes then combine the same NRED partials with the same butterfly.
 // `mb` points at the two mbarriers (one per reduction kind), `par` at their phase parities.
 // ---------------------------------------------------------------------------------------
+// the NRED partials at `r`, added in four interleaved chains in a fixed order (broadcast loads)
+template <int NRED, int NREDP>
+__device__ __forceinline__ float sum_partials(const float* r) {
+    const float4* r4 = reinterpret_cast<const float4*>(r);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int q = 0; q < NREDP / 4; q++) {
+        const float4 v = r4[q];
+        acc.x += v.x;
+        if (4 * q + 1 < NRED) acc.y += v.y;
+        if (4 * q + 2 < NRED) acc.z += v.z;
+        if (4 * q + 3 < NRED) acc.w += v.w;
+    }
+    return (acc.x + acc.y) + (acc.z + acc.w);
+}
+__device__ __forceinline__ float sum4(const float* r) { const float4 v = *reinterpret_cast<const float4*>(r); return (v.x + v.y) + (v.z + v.w); }
+__device__ __forceinline__ double sum4(const double* r) {
+    const double2 a = reinterpret_cast<const double2*>(r)[0], b = reinterpret_cast<const double2*>(r)[1];
+    return (a.x + a.y) + (b.x + b.y);
+}
+template <int NRED, int NREDP>
+__device__ __forceinline__ double sum_partials(const double* r) {
+    const double2* r2 = reinterpret_cast<const double2*>(r);
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+    for (int q = 0; q < NREDP / 2; q++) {
+        const double2 v = r2[q];
+        if (2 * q < NRED) acc[(2 * q) & 3] += v.x;
+        if (2 * q + 1 < NRED) acc[(2 * q + 1) & 3] += v.y;
+    }
+    return (acc[0] + acc[1]) + (acc[2] + acc[3]);
+}
+
 template <class CF>
-__device__ __forceinline__ float cluster_sum(float* red, uint64_t* mb, unsigned (&par)[2], int buf,
-                                             float val, unsigned rank, unsigned halo_bytes) {
+__device__ __forceinline__ typename CF::T cluster_sum(typename CF::T* red, uint64_t* mb, unsigned (&par)[2], int buf,
+                                                      typename CF::T val, unsigned rank, unsigned halo_bytes) {
+    using T = typename CF::T;
     constexpr int CL = CF::CL, NW = CF::NW, NRED = CF::NRED;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const float w = warp_sum(val);
-    float* slot = red + buf * CF::NREDP + rank * NW + warp;
+    const T w = warp_sum(val);
+    T* slot = red + buf * CF::NREDP + rank * NW + warp;
     if constexpr (CL == 1) {
         if (lane == 0) *slot = w;
         __syncthreads();
-        const float4* r4 = reinterpret_cast<const float4*>(red + buf * CF::NREDP);
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);      // four interleaved chains, fixed order
-#pragma unroll
-        for (int q = 0; q < CF::NREDP / 4; q++) {
-            const float4 v = r4[q];
-            acc.x += v.x;
-            if (4 * q + 1 < NRED) acc.y += v.y;
-            if (4 * q + 2 < NRED) acc.z += v.z;
-            if (4 * q + 3 < NRED) acc.w += v.w;
-        }
-        return (acc.x + acc.y) + (acc.z + acc.w);
+        return sum_partials<NRED, CF::NREDP>(red + buf * CF::NREDP);
     } else {
-        if (threadIdx.x == 0) mbar_arrive_expect_tx(mb + buf, (unsigned)NRED * 4u + halo_bytes);
-        if (lane < CL) st_async_f32(mapa_u32(smem_u32(slot), (unsigned)lane), w, mapa_u32(smem_u32(mb + buf), (unsigned)lane));
+        if (threadIdx.x == 0) mbar_arrive_expect_tx(mb + buf, (unsigned)NRED * (unsigned)sizeof(T) + halo_bytes);
+        if (lane < CL) st_async(mapa_u32(smem_u32(slot), (unsigned)lane), w, mapa_u32(smem_u32(mb + buf), (unsigned)lane));
         mbar_wait(mb + buf, par[buf]);
         par[buf] ^= 1u;
-        const float4* r4 = reinterpret_cast<const float4*>(red + buf * CF::NREDP);
         if constexpr (NRED <= 64) {
             // every lane adds all NRED partials itself (broadcast LDS.128, four interleaved chains, fixed
             // order -> the same bits in every lane of every CTA): shorter than a second 5-level shuffle
             // tree (measured N=128, CL=8: 1.74 -> 1.35 us per iteration)
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int q = 0; q < CF::NREDP / 4; q++) {
-                const float4 v = r4[q];
-                acc.x += v.x;
-                if (4 * q + 1 < NRED) acc.y += v.y;
-                if (4 * q + 2 < NRED) acc.z += v.z;
-                if (4 * q + 3 < NRED) acc.w += v.w;
-            }
-            return (acc.x + acc.y) + (acc.z + acc.w);
+            return sum_partials<NRED, CF::NREDP>(red + buf * CF::NREDP);
         } else {
-            // many partials (CL = 16 with 8 warps): one float4 per lane, then the butterfly
-            static_assert(NRED % 4 == 0 && NRED <= 128, "one float4 per lane");
-            float acc = 0.f;
-            if (lane < NRED / 4) { const float4 v = r4[lane]; acc = (v.x + v.y) + (v.z + v.w); }
+            // many partials (CL = 16 with 8 warps): four per lane, then the butterfly
+            static_assert(NRED % 4 == 0 && NRED <= 128, "four partials per lane");
+            T acc = T(0);
+            if (lane < NRED / 4) {
+                acc = sum4(red + buf * CF::NREDP + 4 * lane);
+            }
             return warp_sum(acc);
         }
     }
@@ -687,9 +761,12 @@ __device__ __forceinline__ float sys_poll_tagged(const uint2* src, unsigned tag)
 // locally and need no further exchange.
 // ---------------------------------------------------------------------------------------
 template <class CF, bool SPLIT = false>
-__device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, float* lam_g, int N,
-                                         unsigned max_iter, float exit_tol, unsigned* d_iters,
+__device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>& R, typename CF::T* lam_g, int N,
+                                         unsigned max_iter, typename CF::T exit_tol, unsigned* d_iters,
                                          uint8_t* d_exit, const SplitCtx* X = nullptr) {
+    using T = typename CF::T;
+    using T2 = typename CF::T2;
+    static_assert(!SPLIT || CF::F32, "the knot-range split mailboxes carry fp32 values");
     constexpr int S = 14, KPC = CF::KPC, CL = CF::CL, PR = CF::PR, PK = CF::PK, VK = CF::VK;
     constexpr int LPK = CF::LPK, RPT = CF::RPT;
     const int tid = threadIdx.x;
@@ -706,15 +783,15 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     unsigned gseq[2] = {SPLIT ? X->epoch : 0u, SPLIT ? X->epoch : 0u};
     const int sl = g + 1;
 
-    float* pv = smem + CF::oPv;
-    float* rv = smem + CF::oRv;
-    float* hal = smem + CF::oHal;   // [phase][side][16]; side 0: pushed by my LEFT neighbour CTA
-    float* red = smem + CF::oRed;
+    T* pv = smem + CF::oPv;
+    T* rv = smem + CF::oRv;
+    T* hal = smem + CF::oHal;   // [phase][side][16]; side 0: pushed by my LEFT neighbour CTA
+    T* red = smem + CF::oRed;
     uint64_t* mb = reinterpret_cast<uint64_t*>(smem + CF::oMb);
     unsigned par[2] = {0u, 0u};
-    const unsigned hb = (CL > 1) ? ((has_l ? 56u : 0u) + (has_r ? 56u : 0u)) : 0u;   // halo bytes per phase
+    const unsigned hb = (CL > 1) ? ((has_l ? 14u * (unsigned)sizeof(T) : 0u) + (has_r ? 14u * (unsigned)sizeof(T) : 0u)) : 0u;   // halo bytes per phase
     if (CL > 1 && tid == 0) { mbar_init(mb, 1); mbar_init(mb + 1, 1); fence_mbar_init_cluster(); }
-    const float* myP = smem + CF::oP + sl * PK;
+    const T* myP = smem + CF::oP + sl * PK;
     constexpr bool TM = CF::TM;
     constexpr int TCH = CF::TCH;
     uint32_t* tm_word = reinterpret_cast<uint32_t*>(smem + CF::oTm);
@@ -725,56 +802,67 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     }
 
     // y(rows) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
-    auto s_mv = [&](const float* vec, float (&y)[RPT]) {
-        float2 xl[7], xd[7], xr[7];
+    auto s_mv = [&](const T* vec, T (&y)[RPT]) {
+        T2 xl[7], xd[7], xr[7];
         ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
 #pragma unroll
         for (int j = 0; j < RPT; j++) {
-            const float2 a = dot14_acc(R.Sl[j], xl, splat(0.f)), b = dot14_acc(R.Sd[j], xd, splat(0.f)),
-                         c = dot14_acc(R.Sr[j], xr, splat(0.f));
+            const T2 a = dot14_acc(R.Sl[j], xl, splat(T(0))), b = dot14_acc(R.Sd[j], xd, splat(T(0))),
+                         c = dot14_acc(R.Sr[j], xr, splat(T(0)));
             y[j] = (hsum(a) + hsum(b)) + hsum(c);
         }
     };
     // same with the Pinv rows from shared memory (row = [Pd | Pl | Pr | pad])
-    auto p_mv = [&](const float* vec, float (&y)[RPT]) {
-        float2 xl[7], xd[7], xr[7];
+    auto p_mv = [&](const T* vec, T (&y)[RPT]) {
+        T2 xl[7], xd[7], xr[7];
         ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
 #pragma unroll
         for (int j = 0; j < RPT; j++) {
-            const float4* q4 = reinterpret_cast<const float4*>(myP + rm.row[j] * PR);
-            float2 acc[3] = {splat(0.f), splat(0.f), splat(0.f)};
+            T2 acc[3] = {splat(T(0)), splat(T(0)), splat(T(0))};
+            if constexpr (CF::F32) {
+                const float4* q4 = reinterpret_cast<const float4*>(myP + rm.row[j] * PR);
 #pragma unroll
-            for (int q = 0; q < 11; q++) {
-                const float4 u = q4[q];
-                // floats 4q .. 4q+3 of the row: pairs 2q, 2q+1 of 21 (Pd 0-6, Pl 7-13, Pr 14-20)
+                for (int q = 0; q < 11; q++) {
+                    const float4 u = q4[q];
+                    // floats 4q .. 4q+3 of the row: pairs 2q, 2q+1 of 21 (Pd 0-6, Pl 7-13, Pr 14-20)
 #pragma unroll
-                for (int h = 0; h < 2; h++) {
-                    const int pi = 2 * q + h;
-                    if (pi < 21) {
-                        const int part = pi / 7, w = pi % 7;
-                        const float2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
-                        acc[part] = fma2(h ? f2(u.z, u.w) : f2(u.x, u.y), x, acc[part]);
+                    for (int h = 0; h < 2; h++) {
+                        const int pi = 2 * q + h;
+                        if (pi < 21) {
+                            const int part = pi / 7, w = pi % 7;
+                            const T2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
+                            acc[part] = fma2(h ? f2(u.z, u.w) : f2(u.x, u.y), x, acc[part]);
+                        }
                     }
                 }
+            } else {   // doubles: one pair per 16 B load, same order
+                const T2* q2 = reinterpret_cast<const T2*>(myP + rm.row[j] * PR);
+#pragma unroll
+                for (int pi = 0; pi < 21; pi++) {
+                    const int part = pi / 7, w = pi % 7;
+                    const T2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
+                    acc[part] = fma2(q2[pi], x, acc[part]);
+                }
             }
-            y[j] = rm.ok[j] ? (hsum(acc[1]) + hsum(acc[0])) + hsum(acc[2]) : 0.f;
+            y[j] = rm.ok[j] ? (hsum(acc[1]) + hsum(acc[0])) + hsum(acc[2]) : T(0);
         }
     };
     // same rows from tensor memory: chunk (part, w) = column pair w of all my RPT rows of block `part`
     // (0 Pd, 1 Pl, 2 Pr); the accumulation order per row is the one of p_mv -> identical bits.
     // Loads run one chunk ahead of the FFMA2s; shared memory only delivers the three x vectors.
-    auto p_mv_tm = [&](const float* vec, float (&y)[RPT]) {
+    auto p_mv_tm = [&](const T* vec, T (&y)[RPT]) {
+      if constexpr (TM) {
         constexpr int WPC = CF::TWPC, NCH = CF::TNCH;
         TmemChunk<TCH> buf[2];
-        float part_sum[RPT];
+        T part_sum[RPT];
         buf[0].ld(tcol);
 #pragma unroll
         for (int part = 0; part < 3; part++) {
-            float2 x[7];
+            T2 x[7];
             ld14_v4(x, vec + (sl + (part == 0 ? 0 : (part == 1 ? -1 : 1))) * VK);
-            float2 acc[RPT];
+            T2 acc[RPT];
 #pragma unroll
-            for (int j = 0; j < RPT; j++) acc[j] = splat(0.f);
+            for (int j = 0; j < RPT; j++) acc[j] = splat(T(0));
 #pragma unroll
             for (int w = 0; w < 7; w++) {
                 const int pi = part * 7 + w, c = pi / WPC, o = (pi % WPC) * 2 * RPT;
@@ -790,23 +878,24 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             for (int j = 0; j < RPT; j++) {
                 if (part == 0) part_sum[j] = hsum(acc[j]);
                 else if (part == 1) part_sum[j] = hsum(acc[j]) + part_sum[j];
-                else y[j] = rm.ok[j] ? part_sum[j] + hsum(acc[j]) : 0.f;
+                else y[j] = rm.ok[j] ? part_sum[j] + hsum(acc[j]) : T(0);
             }
         }
+      }
     };
-    auto pinv_mv = [&](const float* vec, float (&y)[RPT]) { if constexpr (TM) p_mv_tm(vec, y); else p_mv(vec, y); };
-    auto put = [&](float* dst, const float (&v)[RPT]) {        // my rows of a 16-float vector slot
+    auto pinv_mv = [&](const T* vec, T (&y)[RPT]) { if constexpr (TM) p_mv_tm(vec, y); else p_mv(vec, y); };
+    auto put = [&](T* dst, const T (&v)[RPT]) {        // my rows of a 16-T vector slot
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) dst[rm.row[j]] = v[j];
     };
-    // my rows -> a 16-float slot of a neighbour CTA, completing bytes on ITS mbarrier `buf`
-    auto push = [&](float* local_dst, unsigned dst_rank, int buf, const float (&v)[RPT]) {
+    // my rows -> a 16-T slot of a neighbour CTA, completing bytes on ITS mbarrier `buf`
+    auto push = [&](T* local_dst, unsigned dst_rank, int buf, const T (&v)[RPT]) {
         const uint32_t ra = mapa_u32(smem_u32(local_dst), dst_rank), rb = mapa_u32(smem_u32(mb + buf), dst_rank);
 #pragma unroll
-        for (int j = 0; j < RPT; j++) if (rm.ok[j]) st_async_f32(ra + 4u * rm.row[j], v[j], rb);
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) st_async(ra + (unsigned)sizeof(T) * rm.row[j], v[j], rb);
     };
     // my rows -> mailbox [phase][side] of rank `dst` (another GPU), tagged
-    auto gpush = [&](int phase, int side, unsigned dst, unsigned tag, const float (&v)[RPT]) {
+    auto gpush = [&](int phase, int side, unsigned dst, unsigned tag, const T (&v)[RPT]) {
         uint2* m = X->mail[dst] + SPLIT_HAL0 + (phase * 2 + side) * 16;
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) sys_store_tagged(m + rm.row[j], v[j], tag);
@@ -815,7 +904,7 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
         return sys_poll_tagged(X->mail[X->grank] + SPLIT_HAL0 + (phase * 2 + side) * 16 + r, tag);
     };
     // boundary rows of the neighbour RANKS -> my halo slots (pre-loop exchanges, phases 2..4)
-    auto gpull_rows = [&](int phase, unsigned tag, float* left_slot, float* right_slot) {
+    auto gpull_rows = [&](int phase, unsigned tag, T* left_slot, T* right_slot) {
 #pragma unroll
         for (int j = 0; j < RPT; j++) {
             if (!rm.ok[j]) continue;
@@ -825,41 +914,41 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
         }
     };
     // all-reduce of the per-rank totals (w is already identical in every thread of this cluster)
-    auto gsum = [&](int buf, unsigned tag, float w) {
+    auto gsum = [&](int buf, unsigned tag, T w) {
         if (rank == 0 && tid < (int)X->world) sys_store_tagged(X->mail[tid] + buf * SPLIT_MAXW + X->grank, w, tag);
         const int lane = tid & 31;
-        float v = 0.f;
+        T v = T(0);
         if (lane < (int)X->world) v = sys_poll_tagged(X->mail[X->grank] + buf * SPLIT_MAXW + lane, tag);
         __syncwarp();
         return warp_sum(v);
     };
-    auto dotp = [&](const float (&a)[RPT], const float (&b)[RPT]) {
-        float d = 0.f;
+    auto dotp = [&](const T (&a)[RPT], const T (&b)[RPT]) {
+        T d = T(0);
 #pragma unroll
-        for (int j = 0; j < RPT; j++) d = fmaf(a[j], b[j], d);   // invalid slots hold zeros
+        for (int j = 0; j < RPT; j++) d = fm(a[j], b[j], d);   // invalid slots hold zeros
         return d;
     };
 
-    float* hl_p = pv;                        // left halo slot
-    float* hr_p = pv + (KPC + 1) * VK;       // right halo slot
-    float* hl_r = rv;
-    float* hr_r = rv + (KPC + 1) * VK;
-    const float zero[RPT] = {};
+    T* hl_p = pv;                        // left halo slot
+    T* hr_p = pv + (KPC + 1) * VK;       // right halo slot
+    T* hl_r = rv;
+    T* hr_r = rv + (KPC + 1) * VK;
+    const T zero[RPT] = {};
 
     // ---- r = gamma - S lambda0 --------------------------------------------------------------
-    float lam[RPT], rr[RPT], pp[RPT], rt[RPT], y[RPT];
+    T lam[RPT], rr[RPT], pp[RPT], rt[RPT], y[RPT];
 #pragma unroll
-    for (int j = 0; j < RPT; j++) lam[j] = (valid && rm.ok[j]) ? lam_g[(size_t)k * S + rm.row[j]] : 0.f;
+    for (int j = 0; j < RPT; j++) lam[j] = (valid && rm.ok[j]) ? lam_g[(size_t)k * S + rm.row[j]] : T(0);
     put(pv + sl * VK, lam);
     if (first_g) {
         const bool ok = (k0 >= 1 && k0 - 1 < N);
 #pragma unroll
-        for (int j = 0; j < RPT; j++) if (rm.ok[j]) hl_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 - 1) * S + rm.row[j]] : 0.f;
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) hl_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 - 1) * S + rm.row[j]] : T(0);
     }
     if (last_g) {
         const bool ok = (k0 + KPC < N);
 #pragma unroll
-        for (int j = 0; j < RPT; j++) if (rm.ok[j]) hr_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 + KPC) * S + rm.row[j]] : 0.f;
+        for (int j = 0; j < RPT; j++) if (rm.ok[j]) hr_p[rm.row[j]] = ok ? lam_g[(size_t)(k0 + KPC) * S + rm.row[j]] : T(0);
     }
     const unsigned tg0 = SPLIT ? X->epoch + 1u : 0u;     // tag of the three pre-loop exchanges
     if (SPLIT) {                                         // warm-start rows of the neighbour ranks
@@ -870,14 +959,14 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     __syncthreads();
     s_mv(pv, y);
 #pragma unroll
-    for (int j = 0; j < RPT; j++) rr[j] = rm.ok[j] ? R.gamma[j] - y[j] : 0.f;
+    for (int j = 0; j < RPT; j++) rr[j] = rm.ok[j] ? R.gamma[j] - y[j] : T(0);
     put(rv + sl * VK, rr);
     if (first_g) { if (has_l) put(map_rank<CL>(hr_r, rank - 1), rr); else if (gl) gpush(3, 1, X->grank - 1, tg0, rr); else put(hl_r, zero); }
     if (last_g)  { if (has_r) put(map_rank<CL>(hl_r, rank + 1), rr); else if (gr) gpush(3, 0, X->grank + 1, tg0, rr); else put(hr_r, zero); }
     if (SPLIT) gpull_rows(3, tg0, hl_r, hr_r);
     cluster_sync_all<CL>();
 
-    if (TM) {   // PROW is final (barrier above): move my Pinv rows into tensor memory
+    if constexpr (TM) {   // PROW is final (barrier above): move my Pinv rows into tensor memory
         tmem_fence_after_sync();
         const int warp = tid >> 5;
         tcol = *tm_word + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * CF::TPT);
@@ -890,8 +979,8 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
                 const int colofs = (part == 0 ? CF::cD : (part == 1 ? CF::cL : CF::cR)) + 2 * w;
 #pragma unroll
                 for (int j = 0; j < RPT; j++) {
-                    float2 v = f2(0.f, 0.f);
-                    if (pi < 21) v = *reinterpret_cast<const float2*>(myP + rm.row[j] * PR + colofs);
+                    T2 v = f2(T(0), T(0));
+                    if (pi < 21) v = *reinterpret_cast<const T2*>(myP + rm.row[j] * PR + colofs);
                     ch.q[u * 2 * RPT + 2 * j] = __float_as_uint(v.x); ch.q[u * 2 * RPT + 2 * j + 1] = __float_as_uint(v.y);
                 }
             }
@@ -907,7 +996,7 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
     if (first_g) { if (has_l) push(hr_p, rank - 1, 1, pp); else if (gl) gpush(4, 1, X->grank - 1, tg0, pp); else put(hl_p, zero); }
     if (last_g)  { if (has_r) push(hl_p, rank + 1, 1, pp); else if (gr) gpush(4, 0, X->grank + 1, tg0, pp); else put(hr_p, zero); }
     if (SPLIT) gpull_rows(4, tg0, hl_p, hr_p);
-    float eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+    T eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
     if (SPLIT) { eta = gsum(1, ++gseq[1], eta); __syncthreads(); }
 
     unsigned iter = 0;
@@ -923,20 +1012,20 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             if (first_g && gl) gpush(0, 1, X->grank - 1, gseq[0] + 1, y);
             if (last_g && gr)  gpush(0, 0, X->grank + 1, gseq[0] + 1, y);
         }
-        float v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
+        T v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
         if (SPLIT) v = gsum(0, ++gseq[0], v);
-        if (v == 0.f) { max_iter_exit = false; break; }
-        const float alpha = eta / v;
+        if (v == T(0)) { max_iter_exit = false; break; }
+        const T alpha = eta / v;
 #pragma unroll
-        for (int j = 0; j < RPT; j++) { lam[j] = fmaf(alpha, pp[j], lam[j]); rr[j] = fmaf(-alpha, y[j], rr[j]); }
+        for (int j = 0; j < RPT; j++) { lam[j] = fm(alpha, pp[j], lam[j]); rr[j] = fm(-alpha, y[j], rr[j]); }
         put(rv + sl * VK, rr);
         if (CL > 1) {
 #pragma unroll
             for (int j = 0; j < RPT; j++) {
                 if (!rm.ok[j]) continue;
                 const int r = rm.row[j];
-                if (first_g && has_l) hl_r[r] = fmaf(-alpha, hal[(0 * 2 + 0) * VK + r], hl_r[r]);
-                if (last_g && has_r)  hr_r[r] = fmaf(-alpha, hal[(0 * 2 + 1) * VK + r], hr_r[r]);
+                if (first_g && has_l) hl_r[r] = fm(-alpha, hal[(0 * 2 + 0) * VK + r], hl_r[r]);
+                if (last_g && has_r)  hr_r[r] = fm(-alpha, hal[(0 * 2 + 1) * VK + r], hr_r[r]);
             }
         }
         if (SPLIT) {
@@ -944,8 +1033,8 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             for (int j = 0; j < RPT; j++) {
                 if (!rm.ok[j]) continue;
                 const int r = rm.row[j];
-                if (first_g && gl) hl_r[r] = fmaf(-alpha, gpull(0, 0, r, gseq[0]), hl_r[r]);
-                if (last_g && gr)  hr_r[r] = fmaf(-alpha, gpull(0, 1, r, gseq[0]), hr_r[r]);
+                if (first_g && gl) hl_r[r] = fm(-alpha, gpull(0, 0, r, gseq[0]), hl_r[r]);
+                if (last_g && gr)  hr_r[r] = fm(-alpha, gpull(0, 1, r, gseq[0]), hr_r[r]);
             }
         }
         __syncthreads();
@@ -959,21 +1048,21 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             if (first_g && gl) gpush(1, 1, X->grank - 1, gseq[1] + 1, rt);
             if (last_g && gr)  gpush(1, 0, X->grank + 1, gseq[1] + 1, rt);
         }
-        float eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+        T eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
         if (SPLIT) eta_new = gsum(1, ++gseq[1], eta_new);
-        if (fabsf(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
-        const float beta = eta_new / eta;
+        if (absT(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
+        const T beta = eta_new / eta;
         eta = eta_new;
 #pragma unroll
-        for (int j = 0; j < RPT; j++) pp[j] = fmaf(beta, pp[j], rt[j]);
+        for (int j = 0; j < RPT; j++) pp[j] = fm(beta, pp[j], rt[j]);
         put(pv + sl * VK, pp);
         if (CL > 1) {
 #pragma unroll
             for (int j = 0; j < RPT; j++) {
                 if (!rm.ok[j]) continue;
                 const int r = rm.row[j];
-                if (first_g && has_l) hl_p[r] = fmaf(beta, hl_p[r], hal[(1 * 2 + 0) * VK + r]);
-                if (last_g && has_r)  hr_p[r] = fmaf(beta, hr_p[r], hal[(1 * 2 + 1) * VK + r]);
+                if (first_g && has_l) hl_p[r] = fm(beta, hl_p[r], hal[(1 * 2 + 0) * VK + r]);
+                if (last_g && has_r)  hr_p[r] = fm(beta, hr_p[r], hal[(1 * 2 + 1) * VK + r]);
             }
         }
         if (SPLIT) {
@@ -981,8 +1070,8 @@ __device__ __forceinline__ void pcg_rows(float* smem, const Rows<CF::RPT>& R, fl
             for (int j = 0; j < RPT; j++) {
                 if (!rm.ok[j]) continue;
                 const int r = rm.row[j];
-                if (first_g && gl) hl_p[r] = fmaf(beta, hl_p[r], gpull(1, 0, r, gseq[1]));
-                if (last_g && gr)  hr_p[r] = fmaf(beta, hr_p[r], gpull(1, 1, r, gseq[1]));
+                if (first_g && gl) hl_p[r] = fm(beta, hl_p[r], gpull(1, 0, r, gseq[1]));
+                if (last_g && gr)  hr_p[r] = fm(beta, hr_p[r], gpull(1, 1, r, gseq[1]));
             }
         }
         __syncthreads();

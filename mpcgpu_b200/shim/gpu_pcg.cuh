@@ -11,8 +11,10 @@
 // (<= 16 CTAs x 128 threads = 16 knots per CTA, 8 lanes per knot) runs the sm_100a
 // cluster/DSMEM PCG of csrc/kkt_device.cuh on the whole horizon; the surplus CTAs of the
 // caller's grid retire immediately (nothing waits on them: there is no grid-wide barrier).
-// Horizons that do not fit one cluster (N > 256, or N without a usable divisor) and
-// T = double fall back to the cooperative one-CTA-per-knot kernel (csrc/refstyle_pcg.cuh).
+// T = double (settings.cuh USE_DOUBLES 1) runs the same cluster kernel instantiated for double while
+// the caller's N CTAs stay co-resident at one 124 KB CTA per SM (N <= 64).
+// Horizons that do not fit one cluster (N > 256, or N without a usable divisor; N > 64 for double)
+// fall back to the cooperative one-CTA-per-knot kernel (csrc/refstyle_pcg.cuh).
 #pragma once
 #include <cstdint>
 #include <cstdio>
@@ -41,7 +43,8 @@ __host__ __device__ constexpr uint32_t cluster_for(uint32_t N) {
 template <typename T, uint32_t S, uint32_t N>
 struct Use {
     static constexpr uint32_t CL = cluster_for(N);
-    static constexpr bool CLUSTER = std::is_same<T, float>::value && S == 14 && CL != 0;
+    static constexpr bool CLUSTER = S == 14 && CL != 0 &&
+        (std::is_same<T, float>::value || (std::is_same<T, double>::value && N <= 64));
     static constexpr uint32_t DIM = CLUSTER ? CL : 1;
 };
 
@@ -52,8 +55,8 @@ struct Use {
 // them in shared memory (3 CTAs per SM).
 __host__ __device__ constexpr int tmem_for(uint32_t N) { return N <= 64 ? MPCB200_PINV_TMEM : 0; }
 
-template <uint32_t N>
-using Tiling = mpcb200::Cfg<KPC, (cluster_for(N) ? cluster_for(N) : 1), 8, tmem_for(N)>;
+template <typename T, uint32_t N>
+using Tiling = mpcb200::Cfg<KPC, (cluster_for(N) ? cluster_for(N) : 1), 8, tmem_for(N), T>;
 
 }  // namespace mpcb200_shim
 
@@ -65,10 +68,10 @@ pcg(T* d_S, T* d_Pinv, T* d_gamma, T* d_lambda, T* d_r, T* d_p, T* d_v_temp, T* 
     uint32_t* d_pcg_iters, bool* d_pcg_exit, uint32_t max_iter, T exit_tol) {
     extern __shared__ float4 pcg_shim_smem4[];
     if constexpr (mpcb200_shim::Use<T, STATE_SIZE_, KNOT_POINTS_>::CLUSTER) {
-        using CF = mpcb200_shim::Tiling<KNOT_POINTS_>;
+        using CF = mpcb200_shim::Tiling<T, KNOT_POINTS_>;
         if (blockIdx.x >= CF::CL) return;            // surplus clusters of the caller's grid
-        float* smem = reinterpret_cast<float*>(pcg_shim_smem4);
-        mpcb200::Rows<CF::RPT> R;
+        T* smem = reinterpret_cast<T*>(pcg_shim_smem4);
+        mpcb200::RowsOf<CF> R;
         mpcb200::load_rows<CF>(smem, R, d_S, d_Pinv, d_gamma, (int)KNOT_POINTS_);
         mpcb200::pcg_rows<CF>(smem, R, d_lambda, (int)KNOT_POINTS_, max_iter, exit_tol, d_pcg_iters,
                               reinterpret_cast<uint8_t*>(d_pcg_exit));
@@ -89,12 +92,14 @@ pcg(T* d_S, T* d_Pinv, T* d_gamma, T* d_lambda, T* d_r, T* d_p, T* d_v_temp, T* 
 template <typename T>
 size_t pcgSharedMemSize(uint32_t state_size, uint32_t knot_points) {
     size_t bytes = sizeof(T) * mpcb200_refstyle::smem_elems<T>(state_size);
-    if (std::is_same<T, float>::value && state_size == 14 && mpcb200_shim::cluster_for(knot_points) != 0) {
+    const bool cluster = state_size == 14 && mpcb200_shim::cluster_for(knot_points) != 0 &&
+                         (std::is_same<T, float>::value || (std::is_same<T, double>::value && knot_points <= 64));
+    if (cluster) {
         const size_t cl = mpcb200_shim::cluster_for(knot_points);
-        // == Cfg<16, cl, 8>::SMEM_BYTES: knot_points is a run-time value here, and the cluster size only
+        // == Cfg<16, cl, 8, ., T>::SMEM_BYTES: knot_points is a run-time value here, and the cluster size only
         // enters through the two partial-sum buffers (NREDP = cl * 4 warps, rounded up to 4)
-        using C1 = mpcb200::Cfg<mpcb200_shim::KPC, 1, 8>;
-        bytes = C1::SMEM_BYTES + sizeof(float) * 2 * (((cl * 4 + 3) & ~size_t(3)) - C1::NREDP);
+        using C1 = mpcb200::Cfg<mpcb200_shim::KPC, 1, 8, 0, T>;
+        bytes = C1::SMEM_BYTES + sizeof(T) * 2 * (((cl * 4 + 3) & ~size_t(3)) - C1::NREDP);
     }
 #if MPCB200_SHIM_HAVE_DIMS
     // the reference launches with more than the 48 KB default and with cluster sizes up to 16:

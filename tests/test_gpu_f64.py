@@ -1,0 +1,163 @@
+"""GPU parity tests (-m gpu) of the fp64 twins (mpcgpu_b200_*_f64; the reference built with
+USE_DOUBLES 1, include/common/settings.cuh:49-57) against the fp64 oracle and the reference's own
+QDLDL (double build) on the same seeded inputs.  Tolerances (fp64):
+  * S / Pinv blocks, gamma, G^-1: 1e-9 relative (Frobenius, per written block) vs the fp64 oracle
+    (two correct fp64 evaluation orders of Gauss-Jordan inverses with entries up to 1/rho);
+  * PCG lambda: 1e-9 relative (widened to 4x the oracle's own evaluation-order noise floor) vs the fp64
+    oracle PCG on identical (S, Pinv, gamma, lambda0) stopped at the same iteration; iteration count within +-1; exit flag equal;
+  * lambda vs the reference QDLDL direct solve of the same system: 1e-4 relative (north_star) at exit
+    tolerance 1e-14 -- fp64 CG, unlike fp32 CG, reaches the direct solve at rho = 1e-3.
+"""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+import mpcgpu_b200 as mg
+from mpcgpu_b200 import synth
+from helpers import S, C, rel, block_rel
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+F = np.float64
+
+
+def lam_tol(N, S64, P64, g64, lam0, iters):
+    """1e-9 relative, widened to 4x the measured distance between the oracle's own two fp64 evaluation
+    orders of the same iterations (CG loses orthogonality once Ritz values converge: at N = 16, 127
+    iterations the two orders are 3e-5 apart; at N = 128, 705 iterations 7e-14)."""
+    a, _, _ = oracle.pcg(S, N, S64, P64, g64, lam0, iters, 0.0, F, mode=0)
+    b, _, _ = oracle.pcg(S, N, S64, P64, g64, lam0, iters, 0.0, F, mode=1)
+    return max(1e-9, 4.0 * rel(a, b))
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=F)).to(DEV)
+
+
+def gen(N, B, seed):
+    d = synth.gen_kkt(N, B, seed=seed)
+    return {k: (np.asarray(v, F) if isinstance(v, np.ndarray) else v) for k, v in d.items()}
+
+
+def gpu_schur(N, d, batch):
+    z = mg.sizes(S, C, N)
+    G, Cm, g, cv = dev(d["G"][:batch]), dev(d["C"][:batch]), dev(d["g"][:batch]), dev(d["c"][:batch])
+    mk = lambda n: torch.full((batch, n), float("nan"), dtype=torch.float64, device=DEV)
+    Sg, Pg, gam = mk(z["S"]), mk(z["S"]), mk(z["gamma"])
+    mg.form_schur_system(S, C, N, G, Cm, g, cv, Sg, Pg, gam, d["rho"], batch=batch)
+    torch.cuda.synchronize()
+    return Sg, Pg, gam, G
+
+
+def gpu_pcg(N, Sg, Pg, gam, lam0, tol, max_iter=10000, batch=1):
+    lam = dev(lam0).clone()
+    it = torch.full((batch,), -1, dtype=torch.int32, device=DEV)
+    ex = torch.full((batch,), 7, dtype=torch.uint8, device=DEV)
+    mg.pcg(S, N, Sg, Pg, gam, lam, it, ex, mg.PcgConfig(pcg_exit_tol=tol, pcg_max_iter=max_iter), batch=batch)
+    torch.cuda.synchronize()
+    return lam.cpu().numpy(), it.cpu().numpy(), ex.cpu().numpy()
+
+
+@pytest.mark.parametrize("N", [1, 2, 3, 16, 17, 32, 33, 64, 100, 128, 129, 256])
+def test_schur_f64_matches_oracle(N):
+    d = gen(N, 2, synth.BASE_SEED + N)
+    Sg, Pg, gam, Gi = gpu_schur(N, d, 2)
+    for b in range(2):
+        ref = oracle.schur(S, C, N, d["G"][b], d["C"][b], d["g"][b], d["c"][b], d["rho"], F)
+        Sn, Pn, gn, Gn = (t.cpu().numpy()[b] for t in (Sg, Pg, gam, Gi))
+        assert np.all(np.isfinite(Sn)) and np.all(np.isfinite(Pn))      # corners written as zeros
+        assert block_rel(S, N, Sn, ref[0]) < 1e-9
+        assert block_rel(S, N, Pn, ref[1]) < 1e-9
+        assert rel(gn, ref[2]) < 1e-9
+        if N > 1:
+            assert rel(Gn, ref[3]) < 1e-9
+        z = Sn.reshape(N, 3, S * S)
+        assert np.all(z[0, 0] == 0) and np.all(z[N - 1, 2] == 0)
+
+
+@pytest.mark.parametrize("N,tol", [(1, 1e-12), (2, 1e-12), (16, 1e-8), (32, 1e-4), (33, 1e-10), (64, 1e-4),
+                                   (64, 1e-14), (100, 1e-8), (128, 1e-4), (128, 1e-14), (256, 1e-6)])
+def test_pcg_f64_matches_oracle(N, tol):
+    d = gen(N, 1, synth.BASE_SEED + 3 * N)
+    S64, P64, g64, _ = oracle.schur(S, C, N, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], F)
+    lam0 = np.zeros((1, S * N), F)
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S64, P64, g64, lam0[0], 10000, tol, F)
+    lam_g, it_g, ex_g = gpu_pcg(N, dev(S64[None]), dev(P64[None]), dev(g64[None]), lam0, tol)
+    assert abs(int(it_g[0]) - it_o) <= 1, (it_g, it_o)
+    assert bool(ex_g[0]) == ex_o
+    lam_s, _, _ = oracle.pcg(S, N, S64, P64, g64, lam0[0], int(it_g[0]), 0.0, F, mode=0)
+    assert rel(lam_g[0], lam_s) < lam_tol(N, S64, P64, g64, lam0[0], int(it_g[0]))
+    if tol <= 1e-14 and N > 2:   # |r.Pinv r| < 1e-14: CG has reached the direct solve (1e-10 leaves 5e-4)
+        assert rel(lam_g[0], oracle.qdldl_solve(S, N, S64, g64)) < 1e-4
+
+
+@pytest.mark.parametrize("N", [8, 64, 128])
+def test_pcg_f64_warm_start_and_max_iter(N):
+    d = gen(N, 1, synth.BASE_SEED + 11 * N)
+    S64, P64, g64, _ = oracle.schur(S, C, N, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], F)
+    lam_star = oracle.qdldl_solve(S, N, S64, g64)
+    rng = np.random.default_rng(N)
+    warm = (lam_star * (1 + 1e-2 * rng.standard_normal(S * N)))[None]
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S64, P64, g64, warm[0], 10000, 1e-6, F)
+    lam_g, it_g, ex_g = gpu_pcg(N, dev(S64[None]), dev(P64[None]), dev(g64[None]), warm, 1e-6)
+    assert abs(int(it_g[0]) - it_o) <= 1 and bool(ex_g[0]) == ex_o
+    lam_s, _, _ = oracle.pcg(S, N, S64, P64, g64, warm[0], int(it_g[0]), 0.0, F, mode=0)
+    assert rel(lam_g[0], lam_s) < lam_tol(N, S64, P64, g64, warm[0], int(it_g[0]))
+    # max_iter exhausted: iters == max_iter, flag = 1 (include/pcg/sqp.cuh:277,289)
+    lam_o, it_o, ex_o = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), 5, 1e-300, F)
+    lam_g, it_g, ex_g = gpu_pcg(N, dev(S64[None]), dev(P64[None]), dev(g64[None]), np.zeros((1, S * N)), 1e-300, max_iter=5)
+    assert it_o == 5 and int(it_g[0]) == 5 and ex_o and bool(ex_g[0])
+    assert rel(lam_g[0], lam_o) < 1e-9
+
+
+@pytest.mark.parametrize("N,B", [(1, 2), (5, 3), (32, 3), (64, 40), (96, 3), (128, 20), (256, 3)])
+def test_fused_f64_matches_two_stage_oracle_and_qdldl(N, B):
+    """kkt_solve_f64 (one launch) == schur_f64 + pcg_f64 (bit-identical lambda, iterations, G^-1), both
+    within tolerance of the fp64 oracle, lambda within 1e-4 of the reference QDLDL solve; the compute_dz
+    epilogue gives the standalone dz kernel's bits and matches the oracle."""
+    d = gen(N, B, synth.BASE_SEED + 7 * N)
+    tol = 1e-14
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    Sg, Pg, gam, Gi2 = gpu_schur(N, d, B)
+    lam2, it2, ex2 = gpu_pcg(N, Sg, Pg, gam, np.zeros((B, S * N)), tol, batch=B)
+    G, Cm, g, cv = dev(d["G"]), dev(d["C"]), dev(d["g"]), dev(d["c"])
+    lam = torch.zeros((B, S * N), dtype=torch.float64, device=DEV)
+    it = torch.full((B,), -1, dtype=torch.int32, device=DEV)
+    ex = torch.full((B,), 7, dtype=torch.uint8, device=DEV)
+    nz = (S + C) * N - C
+    dz_f = torch.full((B, nz), float("nan"), dtype=torch.float64, device=DEV)
+    n0 = mg.launch_count()
+    mg.kkt_solve_dz(S, C, N, G, Cm, g, cv, d["rho"], lam, dz_f, it, ex, cfg, batch=B)
+    assert mg.launch_count() == n0 + 1
+    dz_s = torch.full((B, nz), float("nan"), dtype=torch.float64, device=DEV)
+    mg.compute_dz(S, C, N, G, Cm, g, lam, dz_s, batch=B)
+    torch.cuda.synchronize()
+    assert torch.equal(G, Gi2)
+    assert np.array_equal(it.cpu().numpy(), it2) and np.array_equal(ex.cpu().numpy(), ex2)
+    assert np.array_equal(lam.cpu().numpy(), lam2)
+    assert torch.equal(dz_f, dz_s)
+    # kkt_solve without the epilogue: same lambda
+    G3, lam3 = dev(d["G"]), torch.zeros_like(lam)
+    mg.kkt_solve(S, C, N, G3, Cm, g, cv, d["rho"], lam3, it, ex, cfg, batch=B)
+    torch.cuda.synchronize()
+    assert torch.equal(lam3, lam)
+    lam_h, dz_h, Gi_h = lam.cpu().numpy(), dz_s.cpu().numpy(), G.cpu().numpy()
+    for b in range(min(B, 4)):
+        S64, P64, g64, Gi = oracle.schur(S, C, N, d["G"][b], d["C"][b], d["g"][b], d["c"][b], d["rho"], F)
+        lam_o, it_o, ex_o = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), 10000, tol, F)
+        assert abs(int(it2[b]) - it_o) <= 1 and bool(ex2[b]) == ex_o
+        lam_s, _, _ = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), int(it2[b]), 0.0, F)
+        assert rel(lam_h[b], lam_s) < max(1e-7, lam_tol(N, S64, P64, g64, np.zeros(S * N), int(it2[b])))   # GPU S vs oracle S: 1e-16 x kappa
+        if N > 2:
+            assert rel(lam_h[b], oracle.qdldl_solve(S, N, S64, g64)) < 1e-4
+        assert rel(dz_h[b], oracle.dz(S, C, N, Gi_h[b], d["C"][b], d["g"][b], lam_h[b], F)) < 1e-9
+
+
+def test_f64_rejects_unsupported_sizes():
+    z = mg.sizes(S, C, 512)
+    t = lambda n: torch.zeros(n, dtype=torch.float64, device=DEV)
+    it = torch.zeros(1, dtype=torch.int32, device=DEV)
+    ex = torch.zeros(1, dtype=torch.uint8, device=DEV)
+    with pytest.raises(mg.MpcGpuError):
+        mg.kkt_solve(S, C, 512, t(z["G"]), t(z["C"]), t(z["g"]), t(z["c"]), 1e-3, t(z["lambda"]), it, ex, mg.PcgConfig())

@@ -27,7 +27,7 @@ static void probe() {
     cfg.numAttrs = 2;
     cudaError_t e2 = cudaOccupancyMaxActiveClusters(&ncl_coop, k, &cfg);
     printf("{\"N\": %u, \"pinv_in_tmem\": %d, \"cluster\": %u, \"regs\": %d, \"smem\": %zu, \"ctas_per_sm\": %d, \"max_clusters\": %d, \"max_clusters_coop\": %d, \"err\": [%d, %d], \"needed_clusters\": %u}\n",
-           N, mpcb200_shim::Use<float, 14, N>::CLUSTER ? (int)mpcb200_shim::Tiling<N>::TM : -1, cl, fa.numRegs, smem, per_sm, ncl, ncl_coop, (int)e1, (int)e2, N / cl);
+           N, mpcb200_shim::Use<float, 14, N>::CLUSTER ? (int)mpcb200_shim::Tiling<float, N>::TM : -1, cl, fa.numRegs, smem, per_sm, ncl, ncl_coop, (int)e1, (int)e2, N / cl);
     cudaGetLastError();
 }
 
