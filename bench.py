@@ -193,6 +193,41 @@ def single_solve_latency(torch, mg, N, tol):
     return out
 
 
+def f64_leg(torch, mg, N, B, tol):
+    """The fp64 twins (USE_DOUBLES 1): batched fused solves/s on B instances and one single-solve
+    latency, same synthetic blocks as the fp32 workload converted to double."""
+    from mpcgpu_b200 import synth
+    dev = "cuda"
+    d = synth.gen_kkt_fast(N, B, seed=synth.BASE_SEED)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+    G0, Cm, g, cv = t(d["G"]), t(d["C"]), t(d["g"]), t(d["c"])
+    G = G0.clone()
+    lam = torch.zeros((B, S * N), dtype=torch.float64, device=dev)
+    it = torch.zeros(B, dtype=torch.int32, device=dev); ex = torch.ones(B, dtype=torch.uint8, device=dev)
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    ts = []
+    for rep in range(5):
+        G.copy_(G0); lam.zero_()
+        a0, a1 = ev(), ev()
+        a0.record()
+        mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg, batch=B)
+        a1.record(); torch.cuda.synchronize()
+        if rep >= 2:
+            ts.append(a0.elapsed_time(a1))
+    ms = float(np.mean(ts))
+    iters = it.float().mean().item()
+    G1, l1 = G0[:1].clone(), lam[:1].clone()
+    def reset():
+        G1.copy_(G0[:1]); l1.zero_()
+    us = _graph_time_us(torch, lambda: mg.kkt_solve(S, C, N, G1, Cm[:1], g[:1], cv[:1], d["rho"], l1, it[:1], ex[:1], cfg), reset)
+    flops = N * (F_SCHUR * B + F_ITER * iters * B)
+    return {"dtype": "f64", "knot_points": N, "batch": B, "exit_tol": tol, "kernel_ms": ms,
+            "solves_per_s": B / (ms * 1e-3), "mean_iters": iters, "max_iter_exits": int(ex.sum().item()),
+            "GBps_def_b": 2 * B * def_b_bytes(N) / (ms * 1e-3) / 1e9, "fp64_tflops": flops / (ms * 1e-3) / 1e12,
+            "single_fused_us": us, "single_fused_iters": int(it[0].item())}
+
+
 def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, reps=30):
     """BASELINE.json configs[3]: one N-knot horizon split by knot range over the `world` GPUs
     (NVLink peer mailboxes, no collective call inside the solve).  Stream-timed, max over ranks."""
@@ -383,6 +418,7 @@ def main():
             if not a.no_extras:
                 line["two_stage"] = two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, a.tol, peak)
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
+                line["f64"] = f64_leg(torch, mg, N, min(B, 1024), a.tol)
         if ks is not None:
             line["knot_split"] = ks
         print(json.dumps(line))

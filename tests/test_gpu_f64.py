@@ -59,6 +59,14 @@ def gpu_pcg(N, Sg, Pg, gam, lam0, tol, max_iter=10000, batch=1):
     return lam.cpu().numpy(), it.cpu().numpy(), ex.cpu().numpy()
 
 
+def it_slack(N, S64, P64, g64, lam0, tol, it_o):
+    """+-1 (north_star) wherever the iteration count is a property of the problem; deep into
+    convergence (hundreds of iterations, tol <= 1e-10) the oracle's OWN two fp64 evaluation orders exit
+    at different iterations (N = 96, tol 1e-14: 635 vs 659) -- there the allowance is twice their spread."""
+    _, it_alt, _ = oracle.pcg(S, N, S64, P64, g64, lam0, 10000, tol, F, mode=1)
+    return max(1, 2 * abs(it_alt - it_o))
+
+
 @pytest.mark.parametrize("N", [1, 2, 3, 16, 17, 32, 33, 64, 100, 128, 129, 256])
 def test_schur_f64_matches_oracle(N):
     d = gen(N, 2, synth.BASE_SEED + N)
@@ -84,7 +92,7 @@ def test_pcg_f64_matches_oracle(N, tol):
     lam0 = np.zeros((1, S * N), F)
     lam_o, it_o, ex_o = oracle.pcg(S, N, S64, P64, g64, lam0[0], 10000, tol, F)
     lam_g, it_g, ex_g = gpu_pcg(N, dev(S64[None]), dev(P64[None]), dev(g64[None]), lam0, tol)
-    assert abs(int(it_g[0]) - it_o) <= 1, (it_g, it_o)
+    assert abs(int(it_g[0]) - it_o) <= it_slack(N, S64, P64, g64, lam0[0], tol, it_o), (it_g, it_o)
     assert bool(ex_g[0]) == ex_o
     lam_s, _, _ = oracle.pcg(S, N, S64, P64, g64, lam0[0], int(it_g[0]), 0.0, F, mode=0)
     assert rel(lam_g[0], lam_s) < lam_tol(N, S64, P64, g64, lam0[0], int(it_g[0]))
@@ -146,7 +154,7 @@ def test_fused_f64_matches_two_stage_oracle_and_qdldl(N, B):
     for b in range(min(B, 4)):
         S64, P64, g64, Gi = oracle.schur(S, C, N, d["G"][b], d["C"][b], d["g"][b], d["c"][b], d["rho"], F)
         lam_o, it_o, ex_o = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), 10000, tol, F)
-        assert abs(int(it2[b]) - it_o) <= 1 and bool(ex2[b]) == ex_o
+        assert abs(int(it2[b]) - it_o) <= it_slack(N, S64, P64, g64, np.zeros(S * N), tol, it_o) and bool(ex2[b]) == ex_o
         lam_s, _, _ = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), int(it2[b]), 0.0, F)
         assert rel(lam_h[b], lam_s) < max(1e-7, lam_tol(N, S64, P64, g64, np.zeros(S * N), int(it2[b])))   # GPU S vs oracle S: 1e-16 x kappa
         if N > 2:
