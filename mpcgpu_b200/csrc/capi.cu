@@ -89,6 +89,10 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
         return e ? atoi(e) : -1;      // -1: automatic, 0: never, 1: always
     }();
     const int N = a.N;
+#ifdef MPCB200_MINIMAL   // experiment builds (tools/ab_build.sh): the bench tiling only, a minute of nvcc
+    if (N <= 64) return launch<Cfg<64, 1, 4>, KIND>(a, st);
+    return cudaErrorInvalidValue;
+#else
     const int cl_lat = (N + 15) / 16;
     const bool latency = lat == 1 || (lat != 0 && (long long)a.batch * cl_lat <= 148);
     if (latency) {
@@ -111,6 +115,7 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
     if (N <= 256) return launch<Cfg<64, 4, 8>, KIND>(a, st);
     if (N <= 512) return launch<Cfg<64, 8, 8>, KIND>(a, st);
     return cudaErrorInvalidValue;
+#endif
 }
 
 BatchArgs make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
@@ -371,12 +376,14 @@ int mpcgpu_b200_knotsplit_pcg_f32(uint32_t s, uint32_t knots_local, uint32_t ran
     cudaStream_t st = (cudaStream_t)stream;
     cudaError_t e;
     switch (knots_local) {
+#ifndef MPCB200_MINIMAL
         case 16: e = launch_split<Cfg<16, 1, 8>>(a, (int)ranks_here, st); break;
         case 32: e = launch_split<Cfg<16, 2, 8>>(a, (int)ranks_here, st); break;
         case 64: e = launch_split<Cfg<16, 4, 8>>(a, (int)ranks_here, st); break;
         case 128: e = launch_split<Cfg<16, 8, 8>>(a, (int)ranks_here, st); break;
         case 256: e = launch_split<Cfg<16, 16, 8>>(a, (int)ranks_here, st); break;
         case 512: e = launch_split<Cfg<32, 16, 8>>(a, (int)ranks_here, st); break;
+#endif
         default: return bad("mpcgpu_b200_knotsplit_pcg_f32: knots per rank must be 16, 32, 64, 128, 256 or 512");
     }
     return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_knotsplit_pcg_f32");
