@@ -38,6 +38,7 @@ RUN = os.path.join(REFOUT, "run")            # working directory of the referenc
 HARNESS = os.path.join(RUN, "ref_harness")
 TRACK = os.path.join(RUN, "track_iiwa_pcg_n%d")
 TRACK_KNOTS = (32, 128)
+KKTB = os.path.join(RUN, "kkt_batched_check")   # tools/kkt_batched_check.cu
 SLOT = os.path.join(RUN, "track_slot_%s_n%d")    # tools/track_slot.cu: simulateMPC over the pcg / b200 slot
 
 
@@ -90,6 +91,11 @@ def _build_reference_cuda(force, verbose):
                 continue   # product library not built yet (mpcgpu_b200.build runs first in __graft_entry__.build)
             if force or _stale(SLOT % (name, n), slot_deps):
                 jobs.append((slot_src, SLOT % (name, n), ["-DKNOT_POINTS=%d" % n, "-DSLOT_B200=%d" % flag], bool(flag)))
+    kb_src = os.path.join(root, "tools", "kkt_batched_check.cu")     # batched KKT producer vs the reference kernel
+    kb_deps = deps + [kb_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "kkt_batched.cuh"),
+                      os.path.join(root, "include", "mpcgpu_b200.h")]
+    if os.path.exists(lib) and (force or _stale(KKTB, kb_deps)):
+        jobs.append((kb_src, KKTB, [], True))
     if jobs:   # each is a minute of nvcc on the GRiD dynamics headers: run them side by side
         from concurrent.futures import ThreadPoolExecutor
         with ThreadPoolExecutor(max_workers=min(len(jobs), max(1, (os.cpu_count() or 2) // 2))) as ex:

@@ -125,3 +125,23 @@ def test_closed_loop_tracking_through_the_b200_slot():
     assert out["sqp_iters_mean"] >= 3.0            # PCG slot on the same box: 3.8 (profiles/r1_track_slot.jsonl)
     assert np.isfinite(out["tracking_err_mean"]) and out["tracking_err_mean"] < 0.25   # PCG slot: 0.10
     assert out["final_tracking_err"] < 0.25
+
+
+@pytest.mark.parametrize("N,B", [(8, 5), (32, 40), (64, 300), (128, 64)])
+def test_batched_kkt_producer_matches_reference_kernel_and_feeds_batched_solve(N, B):
+    """SURVEY 8(f) rank 3 / BASELINE.json configs[4] end to end on real IIWA dynamics
+    (tools/kkt_batched_check.cu): b200slot::generate_kkt_submatrices_batched writes, for every one of
+    B perturbed instances, the bits the reference's own generate_kkt_submatrices
+    (include/common/kkt.cuh:22-163) writes for that instance alone; the batched kkt_solve_dz on those
+    blocks equals single-instance solves bit for bit and converges on every instance."""
+    import json
+    exe = os.path.join(RUN, "kkt_batched_check")
+    if not os.path.exists(exe):
+        pytest.fail("oracle/_ref/run/kkt_batched_check missing: run oracle/build.py where /root/reference exists")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+    r = subprocess.run([exe, str(N), str(B), "1e-4"], cwd=RUN, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout[-800:], r.stderr[-500:])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["kkt_mismatches_vs_reference_kernel"] == 0 and out["solve_mismatches_vs_single"] == 0
+    assert out["nonfinite_dz"] == 0 and out["max_iter_exits"] == 0 and out["pcg_iters"]["min"] >= 1
