@@ -125,7 +125,7 @@ def test_fused_f64_matches_two_stage_oracle_and_qdldl(N, B):
     within tolerance of the fp64 oracle, lambda within 1e-4 of the reference QDLDL solve; the compute_dz
     epilogue gives the standalone dz kernel's bits and matches the oracle."""
     d = gen(N, B, synth.BASE_SEED + 7 * N)
-    tol = 1e-14
+    tol = 1e-6
     cfg = mg.PcgConfig(pcg_exit_tol=tol)
     Sg, Pg, gam, Gi2 = gpu_schur(N, d, B)
     lam2, it2, ex2 = gpu_pcg(N, Sg, Pg, gam, np.zeros((B, S * N)), tol, batch=B)
@@ -157,9 +157,21 @@ def test_fused_f64_matches_two_stage_oracle_and_qdldl(N, B):
         assert abs(int(it2[b]) - it_o) <= it_slack(N, S64, P64, g64, np.zeros(S * N), tol, it_o) and bool(ex2[b]) == ex_o
         lam_s, _, _ = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), int(it2[b]), 0.0, F)
         assert rel(lam_h[b], lam_s) < max(1e-6, 10.0 * lam_tol(N, S64, P64, g64, np.zeros(S * N), int(it2[b])))   # GPU S vs oracle S: 1e-16 x kappa
-        if N > 2:
-            assert rel(lam_h[b], oracle.qdldl_solve(S, N, S64, g64)) < 1e-4
         assert rel(dz_h[b], oracle.dz(S, C, N, Gi_h[b], d["C"][b], d["g"][b], lam_h[b], F)) < 1e-9
+    # deep convergence (|r.Pinv r| < 1e-14, hundreds of iterations): lambda reaches the reference's QDLDL
+    # direct solve.  The exit iteration is no longer a property of the problem there (the oracle's own two
+    # evaluation orders differ by several percent), so it is only bounded, not compared.
+    if N > 2:
+        G4, lam4 = dev(d["G"]), torch.zeros_like(lam)
+        mg.kkt_solve(S, C, N, G4, Cm, g, cv, d["rho"], lam4, it, ex, mg.PcgConfig(pcg_exit_tol=1e-14), batch=B)
+        torch.cuda.synchronize()
+        lam4_h, it4 = lam4.cpu().numpy(), it.cpu().numpy()
+        assert int(ex.sum().item()) == 0
+        for b in range(min(B, 4)):
+            S64, P64, g64, _ = oracle.schur(S, C, N, d["G"][b], d["C"][b], d["g"][b], d["c"][b], d["rho"], F)
+            _, it_o, _ = oracle.pcg(S, N, S64, P64, g64, np.zeros(S * N), 10000, 1e-14, F)
+            assert abs(int(it4[b]) - it_o) <= max(2, it_o // 10)
+            assert rel(lam4_h[b], oracle.qdldl_solve(S, N, S64, g64)) < 1e-4
 
 
 def test_f64_rejects_unsupported_sizes():
