@@ -101,6 +101,15 @@ int mpcgpu_b200_kkt_solve_dz_dev_f32(uint32_t state_size, uint32_t control_size,
                                      uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws,
                                      void* stream);
 
+/* Same with one rho PER INSTANCE, d_rho[batch] in device memory: batched SQP iterations adapt every
+ * instance's regularisation on their own (include/pcg/sqp.cuh:375-389), see shim/b200/sqp_batched.cuh. */
+int mpcgpu_b200_kkt_solve_dz_rhovec_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                                        uint32_t batch, float* d_G, const float* d_C, const float* d_g,
+                                        const float* d_c, const float* d_rho, float* d_lambda,
+                                        float* d_dz, uint32_t max_iter, float exit_tol,
+                                        uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws,
+                                        void* stream);
+
 /* compute_dz alone (include/common/dz.cuh:124-133): d_Ginv = d_G after mpcgpu_b200_schur_f32 /
  * kkt_solve, d_C, d_g as given to them, d_lambda the multipliers.  Batched like the rest. */
 int mpcgpu_b200_dz_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,

@@ -23,6 +23,7 @@ struct BatchArgsT {
     unsigned* iters; uint8_t* exits;
     T* dz = nullptr; size_t sdz = 0;   // optional compute_dz epilogue (fused) / output of dz_kernel
     const T* rho_dev = nullptr;        // optional: rho read from device memory (launches replayed from a CUDA graph)
+    size_t rho_stride = 0;             // 0: one rho for the batch; 1: rho_dev[b] per instance (batched SQP iterations)
 };
 using BatchArgs = BatchArgsT<float>;
 
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgsT<
     const int b = blockIdx.x / CF::CL;
     KktPtrs<T> P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
     RowsOf<CF> R;
-    schur_rows<CF>(smem, P, a.N, a.rho_dev ? __ldg(a.rho_dev) : a.rho, R);
+    schur_rows<CF>(smem, P, a.N, a.rho_dev ? __ldg(a.rho_dev + b * a.rho_stride) : a.rho, R);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
     if (a.dz) {   // compute_dz epilogue: lambda and G^-1 were written by this cluster, read back through L2

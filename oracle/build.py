@@ -38,6 +38,7 @@ RUN = os.path.join(REFOUT, "run")            # working directory of the referenc
 HARNESS = os.path.join(RUN, "ref_harness")
 TRACK = os.path.join(RUN, "track_iiwa_pcg_n%d")
 TRACK_KNOTS = (32, 128)
+SQPB = os.path.join(RUN, "sqp_batched_check")   # tools/sqp_batched_check.cu
 KKTB = os.path.join(RUN, "kkt_batched_check")   # tools/kkt_batched_check.cu
 SLOT = os.path.join(RUN, "track_slot_%s_n%d")    # tools/track_slot.cu: simulateMPC over the pcg / b200 slot
 
@@ -96,6 +97,10 @@ def _build_reference_cuda(force, verbose):
                       os.path.join(root, "include", "mpcgpu_b200.h")]
     if os.path.exists(lib) and (force or _stale(KKTB, kb_deps)):
         jobs.append((kb_src, KKTB, [], True))
+    sb_src = os.path.join(root, "tools", "sqp_batched_check.cu")     # batched SQP iterations vs the reference's sequence
+    sb_deps = kb_deps + [sb_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "sqp_batched.cuh")]
+    if os.path.exists(lib) and (force or _stale(SQPB, sb_deps)):
+        jobs.append((sb_src, SQPB, [], True))
     if jobs:   # each is a minute of nvcc on the GRiD dynamics headers: run them side by side
         from concurrent.futures import ThreadPoolExecutor
         with ThreadPoolExecutor(max_workers=min(len(jobs), max(1, (os.cpu_count() or 2) // 2))) as ex:

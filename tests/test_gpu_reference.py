@@ -145,3 +145,24 @@ def test_batched_kkt_producer_matches_reference_kernel_and_feeds_batched_solve(N
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["kkt_mismatches_vs_reference_kernel"] == 0 and out["solve_mismatches_vs_single"] == 0
     assert out["nonfinite_dz"] == 0 and out["max_iter_exits"] == 0 and out["pcg_iters"]["min"] >= 1
+
+
+@pytest.mark.parametrize("N,B,K", [(8, 6, 3), (32, 128, 4), (64, 200, 3)])
+def test_batched_sqp_iterations_follow_the_reference_sequence(N, B, K):
+    """SURVEY 8(f) rank 4 (tools/sqp_batched_check.cu): K SQP iterations of B instances with no host in
+    the loop (batched linearisation, fused solve with per-instance rho, all 8 line-search step lengths of
+    all instances in one launch, device-side step selection / rho adaptation / update) end, for every
+    checked instance, on the bits the reference's own per-instance sequence produces
+    (generate_kkt_submatrices, 8 cooperative ls_gato_compute_merit launches, the host decision of
+    include/pcg/sqp.cuh:352-413)."""
+    import json
+    exe = os.path.join(RUN, "sqp_batched_check")
+    if not os.path.exists(exe):
+        pytest.fail("oracle/_ref/run/sqp_batched_check missing: run oracle/build.py where /root/reference exists")
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+    r = subprocess.run([exe, str(N), str(B), str(K), "1e-4"], cwd=RUN, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stdout[-900:], r.stderr[-500:])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["xu_mismatches_vs_reference_sequence"] == 0 and out["rho_mismatches"] == 0 and out["merit_mismatches"] == 0
+    assert out["nonfinite_xu"] == 0 and out["instances_with_lower_merit"] > 0
