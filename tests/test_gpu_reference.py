@@ -165,4 +165,6 @@ def test_batched_sqp_iterations_follow_the_reference_sequence(N, B, K):
     assert r.returncode == 0, (r.returncode, r.stdout[-900:], r.stderr[-500:])
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["xu_mismatches_vs_reference_sequence"] == 0 and out["rho_mismatches"] == 0 and out["merit_mismatches"] == 0
-    assert out["nonfinite_xu"] == 0 and out["instances_with_lower_merit"] > 0
+    assert out["nonfinite_xu"] == 0
+    if N >= 32:     # (the 8-knot windows start at their optimum: no step length lowers the merit, rho is raised)
+        assert out["instances_with_lower_merit"] == B
