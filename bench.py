@@ -60,22 +60,30 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.index, self.rows, self._stop_evt, self.proc = index, [], threading.Event(), None
 
     def run(self):
-        while not self._stop_evt.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            self._stop_evt.wait(0.2)
+        # ONE nvidia-smi process looping every 50 ms (a process per sample costs ~0.5 s each: a 40 ms timed
+        # region would get a single sample)
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                if line.strip():
+                    self.rows.append([x.strip() for x in line.split(",")])
+                if self._stop_evt.is_set():
+                    break
+        except Exception:
+            pass
 
     def stop(self):
         self._stop_evt.set()
+        if self.proc is not None:
+            try:
+                self.proc.terminate()
+            except Exception:
+                pass
         self.join(timeout=6)
         sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
         mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
@@ -392,6 +400,9 @@ def main():
         ms_per_step = total_ms / a.steps
         ach = B * def_b_bytes(N) / (kern_ms * 1e-3) / 1e9
         flops = N * (F_SCHUR * B + F_ITER * iters.sum())
+        props = torch.cuda.get_device_properties(local)
+        mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0
+        fp32_peak = props.multi_processor_count * 128 * 2 * mhz * 1e6 / 1e12      # FMA lanes x 2 flop x SM clock under load
         prof = os.path.join(ROOT, "profiles", "traffic.json")
         traffic = json.load(open(prof)).get("fused_kernel_dram_bytes_per_launch") if os.path.exists(prof) else None
         line = {"metric": "batched_kkt_solves_per_sec", "value": world * B / (ms_per_step * 1e-3), "unit": "solves/s",
@@ -407,7 +418,8 @@ def main():
                              "bytes_def": "Def. B 3388N-1596 B/instance (SURVEY 8d)",
                              "def_a_equiv_GBps": B * def_a_bytes(N) / (kern_ms * 1e-3) / 1e9,
                              "fp32_tflops": flops / (kern_ms * 1e-3) / 1e12,
-                             "note": "FP32/latency bound by design: arithmetic intensity >= 10 flop/B at 0 iterations"}}
+                             "fp32_peak_tflops": fp32_peak, "fp32_frac": flops / (kern_ms * 1e-3) / 1e12 / fp32_peak,
+                             "note": "FP32/latency bound by design: arithmetic intensity >= 10 flop/B at 0 iterations; fp32_frac = achieved / (SMs x 128 FMA lanes x 2 x measured SM clock)"}}
         if world == 1:
             threads = os.cpu_count() or 1
             sample = max(threads * 8, 256)

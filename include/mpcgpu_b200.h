@@ -140,6 +140,12 @@ int mpcgpu_b200_kkt_solve_dz_f64(uint32_t state_size, uint32_t control_size, uin
                                  const double* d_c, double rho, double* d_lambda, double* d_dz,
                                  uint32_t max_iter, double exit_tol, uint32_t* d_iters,
                                  uint8_t* d_max_iter_exit, void* d_ws, void* stream);
+/* rho read from device memory (one double), cf. mpcgpu_b200_kkt_solve_dz_dev_f32 */
+int mpcgpu_b200_kkt_solve_dz_dev_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
+                                     uint32_t batch, double* d_G, const double* d_C, const double* d_g,
+                                     const double* d_c, const double* d_rho, double* d_lambda,
+                                     double* d_dz, uint32_t max_iter, double exit_tol, uint32_t* d_iters,
+                                     uint8_t* d_max_iter_exit, void* d_ws, void* stream);
 int mpcgpu_b200_dz_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
                        uint32_t batch, const double* d_Ginv, const double* d_C, const double* d_g,
                        const double* d_lambda, double* d_dz, void* stream);

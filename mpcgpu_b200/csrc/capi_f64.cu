@@ -133,6 +133,22 @@ int mpcgpu_b200_kkt_solve_dz_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t ba
     return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_kkt_solve_f64");
 }
 
+int mpcgpu_b200_kkt_solve_dz_dev_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, double* d_G,
+                                     const double* d_C, const double* d_g, const double* d_c, const double* d_rho,
+                                     double* d_lambda, double* d_dz, uint32_t max_iter, double exit_tol,
+                                     uint32_t* d_iters, uint8_t* d_max_iter_exit, void* d_ws, void* stream) {
+    (void)d_ws;
+    if (!sizes_ok(s, c, N, batch)) return bad("mpcgpu_b200_kkt_solve_dz_dev_f64: unsupported sizes (need s=14,c=7,1<=N<=256)");
+    if (!d_G || (N > 1 && !d_C) || !d_g || !d_c || !d_rho || !d_lambda || !d_dz || !d_iters || !d_max_iter_exit) return bad("mpcgpu_b200_kkt_solve_dz_dev_f64: null pointer");
+    Args a = make_args(s, c, N, batch);
+    a.G = d_G; a.C = d_C; a.g = d_g; a.c = d_c; a.rho = 0.0; a.rho_dev = d_rho;
+    a.lambda = d_lambda; a.max_iter = max_iter; a.exit_tol = exit_tol;
+    a.iters = d_iters; a.exits = d_max_iter_exit;
+    a.dz = d_dz; a.sdz = a.sg;
+    cudaError_t e = dispatch<K_FUSED>(a, (cudaStream_t)stream);
+    return e == cudaSuccess ? 0 : fail(e, "mpcgpu_b200_kkt_solve_dz_dev_f64");
+}
+
 int mpcgpu_b200_kkt_solve_f64(uint32_t s, uint32_t c, uint32_t N, uint32_t batch, double* d_G,
                               const double* d_C, const double* d_g, const double* d_c, double rho,
                               double* d_lambda, uint32_t max_iter, double exit_tol, uint32_t* d_iters,

@@ -20,7 +20,7 @@
 //     (MPCGPU_B200_SLOT_GRAPH=0, FINE_GRAINED_TIMING or TIME_LINSYS select the plain stream path).
 // The dynamics-facing kernels are the reference's own, included from where they are:
 // generate_kkt_submatrices (common/kkt.cuh), compute_merit and ls_gato_compute_merit
-// (common/merit.cuh).  fp32 only (settings.cuh USE_DOUBLES 0).
+// (common/merit.cuh).  linsys_t = float or double (settings.cuh USE_DOUBLES; double: knot_points <= 256).
 #pragma once
 #include <cstdint>
 #include <cstdio>
@@ -47,6 +47,24 @@ constexpr float    kMu     = 10.0f;   // merit penalty (include/pcg/sqp.cuh:62,1
 
 inline double us_between(const timespec& a, const timespec& b) {
     return 1e6 * double(b.tv_sec - a.tv_sec) + 1e-3 * double(b.tv_nsec - a.tv_nsec);
+}
+
+// linsys_t = float / double (settings.cuh USE_DOUBLES) -> the _f32 / _f64 entry points of the C ABI
+inline int solve_dz(uint32_t s, uint32_t c, uint32_t N, uint32_t B, float* G, const float* C, const float* g, const float* cv,
+                    float rho, float* lam, float* dz, uint32_t mi, float tol, uint32_t* it, uint8_t* ex, void* ws, void* st) {
+    return mpcgpu_b200_kkt_solve_dz_f32(s, c, N, B, G, C, g, cv, rho, lam, dz, mi, tol, it, ex, ws, st);
+}
+inline int solve_dz(uint32_t s, uint32_t c, uint32_t N, uint32_t B, double* G, const double* C, const double* g, const double* cv,
+                    double rho, double* lam, double* dz, uint32_t mi, double tol, uint32_t* it, uint8_t* ex, void* ws, void* st) {
+    return mpcgpu_b200_kkt_solve_dz_f64(s, c, N, B, G, C, g, cv, rho, lam, dz, mi, tol, it, ex, ws, st);
+}
+inline int solve_dz_dev(uint32_t s, uint32_t c, uint32_t N, uint32_t B, float* G, const float* C, const float* g, const float* cv,
+                        const float* rho, float* lam, float* dz, uint32_t mi, float tol, uint32_t* it, uint8_t* ex, void* ws, void* st) {
+    return mpcgpu_b200_kkt_solve_dz_dev_f32(s, c, N, B, G, C, g, cv, rho, lam, dz, mi, tol, it, ex, ws, st);
+}
+inline int solve_dz_dev(uint32_t s, uint32_t c, uint32_t N, uint32_t B, double* G, const double* C, const double* g, const double* cv,
+                        const double* rho, double* lam, double* dz, uint32_t mi, double tol, uint32_t* it, uint8_t* ex, void* ws, void* st) {
+    return mpcgpu_b200_kkt_solve_dz_dev_f64(s, c, N, B, G, C, g, cv, rho, lam, dz, mi, tol, it, ex, ws, st);
 }
 
 template <typename T>
@@ -146,7 +164,7 @@ template <typename T>
 auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const uint32_t knot_points, float timestep,
                   T* d_eePos_traj, T* d_lambda, T* d_xu, void* d_dynMem_const, pcg_config<T>& config, T& rho,
                   T rho_reset) {
-    static_assert(std::is_same<T, float>::value, "mpcgpu_b200 slot: fp32 only (settings.cuh USE_DOUBLES 0)");
+    static_assert(std::is_same<T, float>::value || std::is_same<T, double>::value, "mpcgpu_b200 slot: linsys_t is float or double");
     using namespace b200slot;
 
     std::vector<int> pcg_iter_vec;
@@ -208,7 +226,7 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
                 take_step_dev<T><<<1, 256, 0, w.main>>>(w.nz, w.ctl + 1, w.dz, d_xu);
                 generate_kkt_submatrices<T><<<knot_points, KKT_THREADS, kkt_smem, w.main>>>(
                     state_size, control_size, knot_points, w.G, w.C, w.g, w.cv, d_dynMem_const, dt, d_eePos_traj, w.xs, d_xu);
-                ok &= mpcgpu_b200_kkt_solve_dz_dev_f32(state_size, control_size, knot_points, 1, w.G, w.C, w.g, w.cv, w.ctl,
+                ok &= solve_dz_dev(state_size, control_size, knot_points, 1, w.G, w.C, w.g, w.cv, w.ctl,
                                                        d_lambda, w.dz, config.pcg_max_iter, config.pcg_exit_tol, w.iters,
                                                        w.flags, nullptr, (void*)w.main) == 0;
                 ok &= cudaEventRecord(w.ev_fork, w.main) == cudaSuccess;
@@ -291,7 +309,7 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
         // 2.+3. Schur complement + preconditioner + PCG + dz recovery: one launch; lambda warm-started
         //    in place, G becomes G^-1 in place, dz = compute_dz(G^-1, C, g, lambda) as the kernel's epilogue
         lap_begin(fine || time_linsys);
-        gpuErrchk((cudaError_t)mpcgpu_b200_kkt_solve_dz_f32(state_size, control_size, knot_points, 1, w.G, w.C, w.g,
+        gpuErrchk((cudaError_t)solve_dz(state_size, control_size, knot_points, 1, w.G, w.C, w.g,
                                                             w.cv, rho, d_lambda, w.dz, config.pcg_max_iter,
                                                             config.pcg_exit_tol, w.iters + solves, w.flags + solves,
                                                             nullptr, nullptr));
