@@ -9,9 +9,14 @@
 #include <cstring>
 #include <string>
 
-#include "capi_internal.h"
-#include "kernels.cuh"
+#include "launch.cuh"
 #include "refstyle_pcg.cuh"
+
+#ifndef MPCB200_MINIMAL
+namespace mpcb200 {
+MPCB200_LAT_CFGS(MPCB200_LAT_DECL)      // defined in capi_lat.cu
+}
+#endif
 
 using namespace mpcb200;
 
@@ -36,41 +41,6 @@ void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 } }
 namespace {
 
-enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2 };
-
-template <class CF, int KIND>
-cudaError_t launch(const BatchArgs& a, cudaStream_t st) {
-    auto kern = (KIND == K_SCHUR) ? schur_kernel<CF> : (KIND == K_PCG) ? pcg_kernel<CF> : fused_kernel<CF>;
-    static thread_local int configured_dev = -1;
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (configured_dev != dev) {
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        if (CF::CL > 8) {
-            e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-            if (e != cudaSuccess) return e;
-        }
-        configured_dev = dev;
-    }
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((unsigned)a.batch * CF::CL, 1, 1);
-    cfg.blockDim = dim3(CF::NT, 1, 1);
-    cfg.dynamicSmemBytes = CF::SMEM_BYTES;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CF::CL;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, kern, a);
-    if (e == cudaSuccess) g_launches.fetch_add(1, std::memory_order_relaxed);
-    return e;
-}
 
 // (KPC, CL, LPK) tiling: N <= KPC*CL.
 //  * throughput tiling (many instances): 64 knots per CTA -- a 64-knot instance lives in ONE SM,
@@ -118,19 +88,7 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
 #endif
 }
 
-BatchArgs make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
-    BatchArgs a;
-    memset(&a, 0, sizeof(a));
-    a.N = (int)N;
-    a.batch = (int)batch;
-    a.sG = (size_t)(s * s + c * c) * N - c * c;
-    a.sC = (size_t)(s * s + s * c) * (N - 1);
-    a.sg = (size_t)(s + c) * N - c;
-    a.sc = (size_t)s * N;
-    a.sS = (size_t)3 * s * s * N;
-    a.sv = (size_t)s * N;
-    return a;
-}
+BatchArgs make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) { return make_batch_args<float>(s, c, N, batch); }
 
 bool sizes_ok(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
     return s == 14 && c == 7 && N >= 1 && N <= 512 && batch >= 1 && batch <= (1u << 24);

@@ -10,8 +10,7 @@
 #include <algorithm>
 #include <cstring>
 
-#include "capi_internal.h"
-#include "kernels.cuh"
+#include "launch.cuh"
 
 using namespace mpcb200;
 using detail::bad;
@@ -20,41 +19,6 @@ using detail::fail;
 namespace {
 
 using Args = BatchArgsT<double>;
-enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2 };
-
-template <class CF, int KIND>
-cudaError_t launch(const Args& a, cudaStream_t st) {
-    auto kern = (KIND == K_SCHUR) ? schur_kernel<CF> : (KIND == K_PCG) ? pcg_kernel<CF> : fused_kernel<CF>;
-    static thread_local int configured_dev = -1;
-    int dev = 0;
-    cudaError_t e = cudaGetDevice(&dev);
-    if (e != cudaSuccess) return e;
-    if (configured_dev != dev) {
-        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES);
-        if (e != cudaSuccess) return e;
-        if (CF::CL > 8) {
-            e = cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
-            if (e != cudaSuccess) return e;
-        }
-        configured_dev = dev;
-    }
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3((unsigned)a.batch * CF::CL, 1, 1);
-    cfg.blockDim = dim3(CF::NT, 1, 1);
-    cfg.dynamicSmemBytes = CF::SMEM_BYTES;
-    cfg.stream = st;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = CF::CL;
-    attr[0].val.clusterDim.y = 1;
-    attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, kern, a);
-    if (e == cudaSuccess) detail::count_launch();
-    return e;
-}
 
 template <int CL> using D = Cfg<16, CL, 16, 0, double>;
 
@@ -69,19 +33,7 @@ cudaError_t dispatch(const Args& a, cudaStream_t st) {
     return cudaErrorInvalidValue;
 }
 
-Args make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
-    Args a;
-    memset(&a, 0, sizeof(a));
-    a.N = (int)N;
-    a.batch = (int)batch;
-    a.sG = (size_t)(s * s + c * c) * N - c * c;
-    a.sC = (size_t)(s * s + s * c) * (N - 1);
-    a.sg = (size_t)(s + c) * N - c;
-    a.sc = (size_t)s * N;
-    a.sS = (size_t)3 * s * s * N;
-    a.sv = (size_t)s * N;
-    return a;
-}
+Args make_args(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) { return make_batch_args<double>(s, c, N, batch); }
 
 bool sizes_ok(uint32_t s, uint32_t c, uint32_t N, uint32_t batch) {
     return s == 14 && c == 7 && N >= 1 && N <= 256 && batch >= 1 && batch <= (1u << 24);
