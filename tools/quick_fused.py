@@ -39,7 +39,8 @@ def child(name):
     ms = float(np.mean(ts))
     print(json.dumps({"build": name, "kernel_ms": round(ms, 4), "min_ms": round(min(ts), 4), "solves_per_s": round(B / ms * 1e3),
                       "iters_sum": int(it.sum().item()), "exits": int(ex.sum().item()),
-                      "lam_sha": hashlib.sha1(lam.cpu().numpy().tobytes()).hexdigest()[:12]}))
+                      "lam_sha": hashlib.sha1(lam.cpu().numpy().tobytes()).hexdigest()[:12],
+                      "ginv_sha": hashlib.sha1(G.cpu().numpy().tobytes()).hexdigest()[:12]}))
 
 
 if __name__ == "__main__":
