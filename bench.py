@@ -198,6 +198,18 @@ def single_solve_latency(torch, mg, N, tol):
         G.copy_(G0); lam.zero_()
     out["fused_us"] = _graph_time_us(torch, lambda: mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg), reset_f)
     out["fused_iters"] = int(it.item())
+    # host-visible latency of one fused solve: launch + kernel + blocking read-back of the iteration count
+    # (what the reference reports as "linsys time": clock_gettime around launch + memcpys, include/pcg/sqp.cuh:269-286)
+    for _ in range(20):
+        reset_f(); mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg); it.item()
+    hv = []
+    for _ in range(200):
+        reset_f(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        mg.kkt_solve(S, C, N, G, Cm, g, cv, d["rho"], lam, it, ex, cfg)
+        it.item()
+        hv.append((time.perf_counter() - t0) * 1e6)
+    out["fused_host_visible_us"] = float(np.median(hv))
     return out
 
 
@@ -362,11 +374,18 @@ def main():
     launches = mg.launch_count() - n0
     total_ms = e0.elapsed_time(e1)
     kern_ms = float(np.mean([x.elapsed_time(y) for x, y in kev]))
+    iters = it.cpu().numpy().astype(np.float64)
+    per_rank = None
     if dist is not None:
+        # every rank solves its OWN perturbed instances (seed + 7919 * rank): iteration counts, hence kernel
+        # times, differ a little by rank; the step time is the max
+        mine = torch.tensor([kern_ms, float(iters.mean())], device=dev, dtype=torch.float64)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"kernel_ms": [round(float(x[0]), 4) for x in allr], "mean_pcg_iters": [round(float(x[1]), 2) for x in allr]}
         tt = torch.tensor([total_ms, kern_ms], device=dev, dtype=torch.float64)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         total_ms, kern_ms = float(tt[0]), float(tt[1])
-    iters = it.cpu().numpy().astype(np.float64)
     assert int(ex.sum().item()) == 0, "PCG hit max_iter in the bench workload"
 
     # ---- e2e through the host-buffer C-ABI solver ------------------------------------------
@@ -431,6 +450,8 @@ def main():
                 line["two_stage"] = two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, a.tol, peak)
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
                 line["f64"] = f64_leg(torch, mg, N, min(B, 1024), a.tol)
+        if per_rank is not None:
+            line["per_rank"] = per_rank
         if ks is not None:
             line["knot_split"] = ks
         print(json.dumps(line))

@@ -240,3 +240,40 @@ def test_oracle_matches_reference_schur_kernel_outputs(name):
     lam_o = oracle.qdldl_solve(S, N, S64, g64)
     assert rel(oracle.bdmv(S, N, S64, lam_ref), g64) < 1e-3
     assert np.all(np.isfinite(lam_o))
+
+
+def test_api_has_no_cpu_path_in_either_precision():
+    """Host tensors (float32 or float64) are refused, and so is any other dtype: there is no CPU fallback."""
+    import torch
+    import mpcgpu_b200 as mg
+    z = mg.sizes(S, C, 4)
+    for dt in (torch.float32, torch.float64, torch.float16):
+        t = lambda n: torch.zeros(n, dtype=dt)
+        it, ex = torch.zeros(1, dtype=torch.int32), torch.zeros(1, dtype=torch.uint8)
+        with pytest.raises(mg.MpcGpuError):
+            mg.kkt_solve(S, C, 4, t(z["G"]), t(z["C"]), t(z["g"]), t(z["c"]), 1e-3, t(z["lambda"]), it, ex, mg.PcgConfig())
+        with pytest.raises(mg.MpcGpuError):
+            mg.form_schur_system(S, C, 4, t(z["G"]), t(z["C"]), t(z["g"]), t(z["c"]), t(z["S"]), t(z["S"]), t(z["gamma"]), 1e-3)
+
+
+def test_cabi_validates_before_touching_the_device():
+    """Unsupported sizes / null pointers come back as cudaErrorInvalidValue (1) with a message, in both
+    precisions, before any CUDA call (so this runs without a GPU)."""
+    from mpcgpu_b200 import build
+    lib = ctypes.CDLL(build.build())
+    lib.mpcgpu_b200_last_error.restype = ctypes.c_char_p
+    u = ctypes.c_uint32
+    one = ctypes.c_void_p(16)     # a non-null pointer that is never dereferenced
+    rc = lib.mpcgpu_b200_kkt_solve_f32(u(14), u(7), u(513), u(1), one, one, one, one, ctypes.c_float(1e-3), one,
+                                       u(10), ctypes.c_float(1e-4), one, one, None, None)
+    assert rc == 1 and b"unsupported sizes" in lib.mpcgpu_b200_last_error()
+    rc = lib.mpcgpu_b200_kkt_solve_f64(u(14), u(7), u(257), u(1), one, one, one, one, ctypes.c_double(1e-3), one,
+                                       u(10), ctypes.c_double(1e-4), one, one, None, None)
+    assert rc == 1 and b"unsupported sizes" in lib.mpcgpu_b200_last_error()
+    rc = lib.mpcgpu_b200_schur_f64(u(12), u(7), u(8), u(1), one, one, one, one, ctypes.c_double(1e-3), one, one, one, None)
+    assert rc == 1
+    rc = lib.mpcgpu_b200_kkt_solve_dz_rhovec_f32(u(14), u(7), u(8), u(2), one, one, one, one, None, one, one,
+                                                 u(10), ctypes.c_float(1e-4), one, one, None, None)
+    assert rc == 1 and b"null pointer" in lib.mpcgpu_b200_last_error()
+    rc = lib.mpcgpu_b200_pcg_f64(u(14), u(8), u(1), one, one, one, None, u(10), ctypes.c_double(1e-4), one, one, None, None)
+    assert rc == 1 and b"null pointer" in lib.mpcgpu_b200_last_error()
