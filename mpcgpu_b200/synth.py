@@ -115,12 +115,16 @@ def gen_kkt(N, batch=1, seed=BASE_SEED, perturb=0.02, s=14, c=7, dtype=np.float3
     }
 
 
-def gen_kkt_fast(N, batch, seed=BASE_SEED, perturb=0.02, s=14, c=7, dtype=np.float32):
+def gen_kkt_fast(N, batch, seed=BASE_SEED, perturb=0.02, s=14, c=7, dtype=np.float32, perturb_seed=None):
     """Vectorised generator for large batches (bench): same structure as :func:`gen_kkt`
-    but one RNG stream for the whole batch (not bit-identical to gen_kkt)."""
+    but one RNG stream for the whole batch (not bit-identical to gen_kkt).
+    perturb_seed: draw the per-instance perturbations from their own stream, so that several shards
+    (one per GPU) share the base trajectory `seed` but hold different perturbed instances of it."""
     nq = s // 2
     rng = np.random.Generator(np.random.PCG64(seed))
     base = _base_trajectory(rng, N, s, c)
+    if perturb_seed is not None:
+        rng = np.random.Generator(np.random.PCG64([int(seed), int(perturb_seed)]))
     rc = r_cost(N)
     sz = sizes(s, c, N)
     Gset, Cset, gset = s * s + c * c, s * s + s * c, s + c
