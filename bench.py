@@ -411,6 +411,17 @@ def main():
     h2d = 4 * B * (hG[0].numel() + hC[0].numel() + hg[0].numel() + hc[0].numel() + S * N)
     d2h = B * (4 * S * N + 4 + 1)
     hs.close()
+    # what bounds e2e: the host->device copy of the KKT blocks.  Measured pinned H2D rate of this box, same process.
+    probe_h = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
+    probe_d = torch.empty_like(probe_h, device=dev)
+    pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    probe_d.copy_(probe_h, non_blocking=True); torch.cuda.synchronize()
+    pe0.record()
+    for _ in range(4):
+        probe_d.copy_(probe_h, non_blocking=True)
+    pe1.record(); torch.cuda.synchronize()
+    h2d_gbps = 4 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+    del probe_h, probe_d
 
     ks = None
     if world > 1 and not a.no_extras and 512 % world == 0 and 512 // world in (64, 128, 256):
@@ -431,7 +442,9 @@ def main():
                 "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(launches),
                 "pcg_iters": {"mean": float(iters.mean()), "min": int(iters.min()), "max": int(iters.max())},
                 "e2e": {"value": world * B / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
-                        "d2h_bytes_per_step": int(d2h)},
+                        "d2h_bytes_per_step": int(d2h), "bound": "pcie_h2d", "h2d_achieved_GBps": h2d / e2e_s / 1e9,
+                        "h2d_peak_GBps": h2d_gbps, "h2d_frac": h2d / e2e_s / 1e9 / h2d_gbps,
+                        "note": "peak = pinned 256 MiB H2D copies timed in this process on rank 0 (ranks share the host's PCIe / memory at N > 1)"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                              "traffic": traffic, "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs)" if how == "measured" else how,
                              "kernel": "fused_kernel (schur_rows + pcg_rows)", "kernel_ms": kern_ms,
