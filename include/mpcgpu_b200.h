@@ -119,7 +119,7 @@ int mpcgpu_b200_dz_f32(uint32_t state_size, uint32_t control_size, uint32_t knot
 /* ---- fp64 twins (linsys_t = double when include/common/settings.cuh:49-57 is built with
  * USE_DOUBLES 1).  Same buffers, layouts, semantics and error behaviour as the _f32 entry points
  * above with every float replaced by double; the same cluster kernels instantiated for double
- * (16 knots per 256-thread CTA, S rows in registers, Pinv rows in shared memory, DFMA pairs).
+ * (16 knots per 128-thread CTA, S rows in registers, Pinv rows in shared memory, DFMA pairs).
  * Supported sizes: state_size 14, control_size 7, 1 <= knot_points <= 256 (16 CTAs per cluster). */
 int mpcgpu_b200_schur_f64(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
                           uint32_t batch, double* d_G, const double* d_C, const double* d_g,

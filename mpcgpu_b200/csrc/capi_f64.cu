@@ -1,13 +1,15 @@
 // capi_f64.cu -- fp64 twins of the C ABI (include/mpcgpu_b200.h), for builds of the reference with
 // USE_DOUBLES 1 (linsys_t = double, include/common/settings.cuh:49-57).
 // The kernels are the templates of kkt_device.cuh / kernels.cuh instantiated for double:
-//   Cfg<16, CL, 16, 0, double>: 16 knots per 256-thread CTA, ONE row per lane (16 lanes per knot, 14
-//   used), S rows (84 registers) stay in registers, Pinv rows in shared memory (no tensor memory: its
-//   columns are 32 bit and the rows would not fit beside a second copy), pair-wise DFMA, the same
-//   st.async + mbarrier cluster reductions carrying 8-byte partials.  N <= 256 (cluster of 16).
+//   Cfg<16, CL, 8, 0, double>: 16 knots per 128-thread CTA, two rows per lane (8 lanes per knot), S rows
+//   (168 registers) stay in registers, Pinv rows in shared memory (no tensor memory: its columns are 32 bit
+//   and the rows would not fit beside a second copy), pair-wise DFMA, the same st.async + mbarrier cluster
+//   reductions carrying 8-byte partials.  N <= 256 (cluster of 16).  MPCGPU_B200_F64_LPK=16 selects the
+//   one-row-per-lane tiling Cfg<16, CL, 16, 0, double> (256 threads, no spills, measured 10 % slower).
 #include "../../include/mpcgpu_b200.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "launch.cuh"
@@ -21,10 +23,21 @@ namespace {
 using Args = BatchArgsT<double>;
 
 template <int CL> using D = Cfg<16, CL, 16, 0, double>;
+template <int CL> using D8 = Cfg<16, CL, 8, 0, double>;     // 8 lanes per knot, two rows per lane (128 threads)
 
 template <int KIND>
 cudaError_t dispatch(const Args& a, cudaStream_t st) {
     const int N = a.N;
+    // measured on B200 (tools/f64_ab.py): 8 lanes per knot 162 k fused solves/s at 1024 x N=64, 16 lanes 148 k
+    static const int lpk = [] { const char* e = getenv("MPCGPU_B200_F64_LPK"); return (e && atoi(e) == 16) ? 16 : 8; }();
+    if (lpk == 8) {
+        if (N <= 16) return launch<D8<1>, KIND>(a, st);
+        if (N <= 32) return launch<D8<2>, KIND>(a, st);
+        if (N <= 64) return launch<D8<4>, KIND>(a, st);
+        if (N <= 128) return launch<D8<8>, KIND>(a, st);
+        if (N <= 256) return launch<D8<16>, KIND>(a, st);
+        return cudaErrorInvalidValue;
+    }
     if (N <= 16) return launch<D<1>, KIND>(a, st);
     if (N <= 32) return launch<D<2>, KIND>(a, st);
     if (N <= 64) return launch<D<4>, KIND>(a, st);
