@@ -30,6 +30,14 @@ cudaError_t dispatch(const Args& a, cudaStream_t st) {
     const int N = a.N;
     // measured on B200 (tools/f64_ab.py): 8 lanes per knot 162 k fused solves/s at 1024 x N=64, 16 lanes 148 k
     static const int lpk = [] { const char* e = getenv("MPCGPU_B200_F64_LPK"); return (e && atoi(e) == 16) ? 16 : 8; }();
+    // throughput tilings (more than one wave of CTAs): 12 knots per 96-thread CTA = 97 KB of shared memory, so
+    // TWO CTAs share an SM and hide each other's reduction latency (measured 1024 x N=64: 187 k vs 162 k solves/s)
+    static const int kpc12 = [] { const char* e = getenv("MPCGPU_B200_F64_KPC12"); return e ? atoi(e) : 1; }();
+    if (kpc12) {
+        if (N > 24 && N <= 36 && (long long)a.batch * 3 > 148) return launch<Cfg<12, 3, 8, 0, double>, KIND>(a, st);
+        if (N > 48 && N <= 72 && (long long)a.batch * 6 > 148) return launch<Cfg<12, 6, 8, 0, double>, KIND>(a, st);
+        if (N > 96 && N <= 132 && (long long)a.batch * 11 > 148) return launch<Cfg<12, 11, 8, 0, double>, KIND>(a, st);
+    }
     if (lpk == 8) {
         if (N <= 16) return launch<D8<1>, KIND>(a, st);
         if (N <= 32) return launch<D8<2>, KIND>(a, st);
