@@ -60,7 +60,11 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
     }();
     const int N = a.N;
 #ifdef MPCB200_MINIMAL   // experiment builds (tools/ab_build.sh): the bench tiling only, a minute of nvcc
+#ifdef MPCB200_MIN64_K     // the tiling under test for N <= 64 (default: the bench tiling)
+    if (N <= 64) return launch<Cfg<MPCB200_MIN64_K, MPCB200_MIN64_C, MPCB200_MIN64_L, MPCB200_MIN64_TM>, KIND>(a, st);
+#else
     if (N <= 64) return launch<Cfg<64, 1, 4>, KIND>(a, st);
+#endif
 #ifdef MPCB200_MIN128_K    // -DMPCB200_MIN128_K=32 -DMPCB200_MIN128_C=4 -DMPCB200_MIN128_L=8: the tiling under test for 64 < N <= 128
     if (N <= 128) return launch<Cfg<MPCB200_MIN128_K, MPCB200_MIN128_C, MPCB200_MIN128_L>, KIND>(a, st);
 #endif

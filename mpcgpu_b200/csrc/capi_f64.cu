@@ -4,8 +4,8 @@
 //   Cfg<16, CL, 8, 0, double>: 16 knots per 128-thread CTA, two rows per lane (8 lanes per knot), S rows
 //   (168 registers) stay in registers, Pinv rows in shared memory (no tensor memory: its columns are 32 bit
 //   and the rows would not fit beside a second copy), pair-wise DFMA, the same st.async + mbarrier cluster
-//   reductions carrying 8-byte partials.  N <= 256 (cluster of 16).  MPCGPU_B200_F64_LPK=16 selects the
-//   one-row-per-lane tiling Cfg<16, CL, 16, 0, double> (256 threads, no spills, measured 10 % slower).
+//   reductions carrying 8-byte partials.  N <= 256 (cluster of 16).  Batches of more than one wave use
+//   Cfg<8, CL, 8, 0, double> (three 64-thread CTAs per SM); MPCGPU_B200_F64_THROUGHPUT_TILING=0 switches it off.
 #include "../../include/mpcgpu_b200.h"
 
 #include <algorithm>
@@ -22,35 +22,26 @@ namespace {
 
 using Args = BatchArgsT<double>;
 
-template <int CL> using D = Cfg<16, CL, 16, 0, double>;
-template <int CL> using D8 = Cfg<16, CL, 8, 0, double>;     // 8 lanes per knot, two rows per lane (128 threads)
+template <int CL> using D8 = Cfg<16, CL, 8, 0, double>;     // latency tiling: 16 knots per 128-thread CTA, two rows per lane
+template <int CL> using T8 = Cfg<8, CL, 8, 0, double>;      // throughput tiling: 8 knots per 64-thread CTA
 
+// Measured on B200 (tools/f64_ab.py, fused solves/s, 1024 x N=64): 16 knots x 16 lanes 148 k, 16 knots x 8 lanes
+// 162 k, 12 knots x 8 lanes (two CTAs per SM) 187 k, 8 knots x 8 lanes (69 KB of shared memory: THREE CTAs per SM
+// hide each other's reduction latency) 208 k; the same order at N = 32 (1.15 M) and N = 128 (108 k).
 template <int KIND>
 cudaError_t dispatch(const Args& a, cudaStream_t st) {
     const int N = a.N;
-    // measured on B200 (tools/f64_ab.py): 8 lanes per knot 162 k fused solves/s at 1024 x N=64, 16 lanes 148 k
-    static const int lpk = [] { const char* e = getenv("MPCGPU_B200_F64_LPK"); return (e && atoi(e) == 16) ? 16 : 8; }();
-    // throughput tilings (more than one wave of CTAs): 12 knots per 96-thread CTA = 97 KB of shared memory, so
-    // TWO CTAs share an SM and hide each other's reduction latency (measured 1024 x N=64: 187 k vs 162 k solves/s)
-    static const int kpc12 = [] { const char* e = getenv("MPCGPU_B200_F64_KPC12"); return e ? atoi(e) : 1; }();
-    if (kpc12) {
-        if (N > 24 && N <= 36 && (long long)a.batch * 3 > 148) return launch<Cfg<12, 3, 8, 0, double>, KIND>(a, st);
-        if (N > 48 && N <= 72 && (long long)a.batch * 6 > 148) return launch<Cfg<12, 6, 8, 0, double>, KIND>(a, st);
-        if (N > 96 && N <= 132 && (long long)a.batch * 11 > 148) return launch<Cfg<12, 11, 8, 0, double>, KIND>(a, st);
+    static const int thr = [] { const char* e = getenv("MPCGPU_B200_F64_THROUGHPUT_TILING"); return e ? atoi(e) : 1; }();
+    if (thr) {      // batches of more than one wave
+        if (N > 16 && N <= 32 && (long long)a.batch * 4 > 148) return launch<T8<4>, KIND>(a, st);
+        if (N > 32 && N <= 64 && (long long)a.batch * 8 > 148) return launch<T8<8>, KIND>(a, st);
+        if (N > 64 && N <= 128 && (long long)a.batch * 16 > 148) return launch<T8<16>, KIND>(a, st);
     }
-    if (lpk == 8) {
-        if (N <= 16) return launch<D8<1>, KIND>(a, st);
-        if (N <= 32) return launch<D8<2>, KIND>(a, st);
-        if (N <= 64) return launch<D8<4>, KIND>(a, st);
-        if (N <= 128) return launch<D8<8>, KIND>(a, st);
-        if (N <= 256) return launch<D8<16>, KIND>(a, st);
-        return cudaErrorInvalidValue;
-    }
-    if (N <= 16) return launch<D<1>, KIND>(a, st);
-    if (N <= 32) return launch<D<2>, KIND>(a, st);
-    if (N <= 64) return launch<D<4>, KIND>(a, st);
-    if (N <= 128) return launch<D<8>, KIND>(a, st);
-    if (N <= 256) return launch<D<16>, KIND>(a, st);
+    if (N <= 16) return launch<D8<1>, KIND>(a, st);
+    if (N <= 32) return launch<D8<2>, KIND>(a, st);
+    if (N <= 64) return launch<D8<4>, KIND>(a, st);
+    if (N <= 128) return launch<D8<8>, KIND>(a, st);
+    if (N <= 256) return launch<D8<16>, KIND>(a, st);
     return cudaErrorInvalidValue;
 }
 

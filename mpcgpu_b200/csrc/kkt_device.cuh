@@ -83,7 +83,7 @@ struct Cfg {
     static constexpr int TCOLS = pow2_at_least(((NW + 3) / 4) * TPT);   // allocation, power of two <= 512
     static_assert(!TM || TCOLS <= 512, "tensor memory has 512 columns");
     static constexpr size_t SMEM_BYTES = sizeof(T) * FLOATS;
-    static constexpr int MIN_CTAS = !F32 ? (SMEM_BYTES <= 113 * 1024 && NT <= 128 ? 2 : 1) : (LPK == 4) ? (256 / NT > 0 ? 256 / NT : 1) : (512 / NT > 0 ? 512 / NT : 1);
+    static constexpr int MIN_CTAS = !F32 ? (SMEM_BYTES <= 75 * 1024 && NT <= 64 ? 3 : SMEM_BYTES <= 113 * 1024 && NT <= 128 ? 2 : 1) : (LPK == 4) ? (256 / NT > 0 ? 256 / NT : 1) : (512 / NT > 0 ? 512 / NT : 1);
     static_assert(LPK == 4 || LPK == 8 || LPK == 16, "4, 8 or 16 lanes per knot");
     static_assert(NT % 32 == 0 && NT <= 1024, "whole warps, <= 1024 threads");
     static_assert(SMEM_BYTES <= 232448, "exceeds the 227 KB per-CTA shared memory of sm_100");
