@@ -23,6 +23,9 @@
 // Qt^-1 rows, then -theta^-1 rows; the (not yet written) Pl / Pr columns hold B, R^-1 and
 // the knot's vectors; a second tile per knot holds A, then phi.
 // Longer horizons use a thread-block cluster of CL CTAs with DSMEM halos.
+// Everything is templated on the scalar type through Cfg<KPC, CL, LPK, TM, T>: T = float (the reference's
+// default linsys_t; pairs are float2 + FFMA2, Pinv rows may live in tensor memory) or T = double
+// (USE_DOUBLES 1; pairs are double2 + two DFMAs, Pinv rows stay in shared memory, LPK may be 16).
 #pragma once
 #include "common.cuh"
 
