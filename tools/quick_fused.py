@@ -18,7 +18,7 @@ def child(name):
     import torch
     import mpcgpu_b200 as mg
     from mpcgpu_b200 import synth
-    S, C, N, B = 14, 7, 64, int(os.environ.get("QF_BATCH", "4096"))
+    S, C, N, B = 14, 7, int(os.environ.get("QF_N", "64")), int(os.environ.get("QF_BATCH", "4096"))
     d = synth.gen_kkt_fast(N, B, seed=synth.BASE_SEED)
     dev = "cuda"
     t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
