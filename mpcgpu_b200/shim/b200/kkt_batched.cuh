@@ -22,6 +22,7 @@
 //   d_eePos + b * ee_stride    end-effector goal, 6 values per knot (ee_stride = 0: one shared goal)
 #pragma once
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <cooperative_groups.h>
 #ifndef MPCGPU_B200_SLOT_COMMON_INCLUDED   // common/kkt.cuh carries no include guard
@@ -29,6 +30,17 @@
 #endif
 
 namespace b200slot {
+
+// threads per block of the batched dynamics-facing kernels.  The reference's device functions stride over
+// blockDim.x, so any multiple of 32 computes the same bits; with thousands of blocks in flight smaller blocks
+// than the reference's 128 (KKT_THREADS, MERIT_THREADS) are faster -- measured on B200, 4096 x N=64:
+// KKT producer 16.6 ms (128) / 15.6 (64) / 18.7 (32); line-search merits: SQP iteration 49 ms (128) / 43 (64) /
+// 37 (32).  Environment variables B200SLOT_KKT_THREADS / B200SLOT_MERIT_THREADS override.
+inline unsigned batched_threads(const char* env, unsigned dflt) {
+    const char* e = getenv(env);
+    const int v = e ? atoi(e) : 0;
+    return (v >= 32 && v <= 1024 && v % 32 == 0) ? (unsigned)v : dflt;
+}
 
 template <typename T>
 __device__ __forceinline__ void block_store(uint32_t n, const T* __restrict__ src, T* __restrict__ dst, T scale) {
@@ -113,7 +125,7 @@ inline cudaError_t launch_kkt_batched(uint32_t state_size, uint32_t control_size
     auto kern = generate_kkt_submatrices_batched<T>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    kern<<<dim3(knot_points - 1, batch), KKT_THREADS, smem, stream>>>(state_size, control_size, knot_points, d_G_dense,
+    kern<<<dim3(knot_points - 1, batch), batched_threads("B200SLOT_KKT_THREADS", 64), smem, stream>>>(state_size, control_size, knot_points, d_G_dense,
                                                                     d_C_dense, d_g, d_c, d_dynMem_const, timestep,
                                                                     d_eePos_traj, ee_stride, d_xs, d_xu, xu_stride);
     return cudaGetLastError();

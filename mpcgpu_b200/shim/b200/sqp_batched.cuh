@@ -192,7 +192,7 @@ struct BatchedSqp {
     // merit of the starting iterates (include/pcg/sqp.cuh:186-193), fixed summation order
     cudaError_t init_merit(const T* d_xs, const T* d_xu, const T* d_ee, size_t ee_stride, void* d_dyn, T dt, T mu,
                            cudaStream_t stream) {
-        ls_merit_batched<T><<<dim3(N, 1, B), MERIT_THREADS, merit_smem(), stream>>>(s, c, N, d_xs, d_xu, nz, d_ee, ee_stride,
+        ls_merit_batched<T><<<dim3(N, 1, B), batched_threads("B200SLOT_MERIT_THREADS", 32), merit_smem(), stream>>>(s, c, N, d_xs, d_xu, nz, d_ee, ee_stride,
                                                                                   mu, dt, d_dyn, dz, kLsAlphas, point);
         init_merit_batched<T><<<B, MERIT_THREADS, 0, stream>>>(N, point, st.merit);
         return cudaGetLastError();
@@ -206,7 +206,7 @@ struct BatchedSqp {
         e = (cudaError_t)mpcgpu_b200_kkt_solve_dz_rhovec_f32(s, c, N, B, G, C, g, cv, st.rho, d_lambda, dz, pcg_max_iter,
                                                             pcg_exit_tol, iters, exits, nullptr, (void*)stream);
         if (e != cudaSuccess) return e;
-        ls_merit_batched<T><<<dim3(N, kLsAlphas, B), MERIT_THREADS, merit_smem(), stream>>>(
+        ls_merit_batched<T><<<dim3(N, kLsAlphas, B), batched_threads("B200SLOT_MERIT_THREADS", 32), merit_smem(), stream>>>(
             s, c, N, d_xs, d_xu, nz, d_ee, ee_stride, mu, dt, d_dyn, dz, 0, point);
         select_step_batched<T><<<B, MERIT_THREADS, 0, stream>>>(N, nz, point, dz, d_xu, nz, st, T(RHO_FACTOR), T(RHO_MIN),
                                                               T(RHO_MAX), rho_reset);
