@@ -70,3 +70,18 @@ def test_knot_range_rules():
     with pytest.raises(mg.MpcGpuError):
         mg.knot_range(24, 0, 2)          # 12 knots per rank: not a supported tile
     assert mg.epoch_stride(mg.PcgConfig(pcg_max_iter=100)) > 2 * 100 + 8
+
+
+def test_rank_shards_share_the_base_trajectory():
+    """bench.py's weak-scaling shards: every rank holds different perturbed instances of the SAME base trajectory
+    (instance 0 of a shard is the unperturbed base), reproducibly."""
+    import numpy as np
+    from mpcgpu_b200 import synth
+    r0 = synth.gen_kkt_fast(8, 6)
+    r1 = synth.gen_kkt_fast(8, 6, perturb_seed=1)
+    r1b = synth.gen_kkt_fast(8, 6, perturb_seed=1)
+    r2 = synth.gen_kkt_fast(8, 6, perturb_seed=2)
+    for k in ("G", "C", "g", "c"):
+        assert np.array_equal(r0[k][0], r1[k][0]) and np.array_equal(r1[k][0], r2[k][0])     # the base
+        assert np.array_equal(r1[k], r1b[k])
+    assert not np.array_equal(r1["C"][1:], r2["C"][1:]) and not np.array_equal(r0["C"][1:], r1["C"][1:])
