@@ -14,9 +14,13 @@ owns its own 4096 instances, no data-path collective.
   roofline  fused kernel alone: Def. B algorithmic bytes / CUDA-event duration
             against the measured HBM peak, plus achieved fp32 TFLOP/s (the kernel is
             FP32/latency bound, not HBM bound -- reported, not hidden)
-  cpu_baseline  the reference's CPU path (oracle Schur restatement + reference QDLDL) on the
-            box's host cores, bounded sample
-  --impl reference   the reference arm: that CPU path with all host threads
+  cpu_baseline  the reference's CPU work on the path = its QDLDL host solve (qdldl_solve_schur,
+            include/qdldl/sqp.cuh:22-49: factor + solve on precomputed CSC values; the reference forms S
+            on the GPU) on all host cores over the same 4096-instance batch, persistent thread pool;
+            `with_schur_restatement` adds the oracle's CPU restatement of the Schur formation
+  --impl reference   the reference arm: that QDLDL host solve with all host threads
+  parity    sampled instances of the timed batch against the oracle / reference QDLDL (oracle/parity.py)
+  warm_start, qdldl_single_core_us: SURVEY 8(d) legs, outside the timed region
 """
 import argparse
 import json
@@ -94,20 +98,78 @@ class ClockSampler(threading.Thread):
                 "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def cpu_reference_run(N, sample, steps, warmup, threads):
-    """The reference's CPU implementation of the path on `threads` host threads."""
+def cpu_reference_run(N, B, steps, warmup, threads, keep=False):
+    """The reference's CPU implementation of the path on `threads` host threads, on the bench batch itself.
+    `value` leg: qdldl_solve_schur (QDLDL_factor + copy + QDLDL_solve, include/qdldl/sqp.cuh:22-49) of all B
+    systems per step on precomputed CSC values / gamma -- the reference's QDLDL slot forms S on the GPU
+    (include/qdldl/linsys_setup.cuh) and only factors / solves on the host, elimination tree once (:193).
+    Threads, workspaces, pattern and tree persist across steps (oracle.CpuPool).  Second leg: the same preceded
+    by the oracle's CPU restatement of that Schur formation (no preconditioner), on a bounded sample."""
     import oracle
     from mpcgpu_b200 import synth
-    d = synth.gen_kkt_fast(N, sample, seed=synth.BASE_SEED)
-    times = []
+    d = synth.gen_kkt_fast(N, B, seed=synth.BASE_SEED)
+    pool = oracle.CpuPool(S, C, N, threads)
+    val, gam = pool.schur_csc(d["G"], d["C"], d["g"], d["c"], d["rho"])        # preparation, not timed
+    walls = []
     for it in range(warmup + steps):
-        lam, wall, t_schur, t_qdldl = oracle.cpu_kkt_solve_batch(
-            S, C, N, d["G"], d["C"], d["g"], d["c"], d["rho"], nthreads=threads)
+        lam, wall = pool.qdldl(val, gam)
         if it >= warmup:
-            times.append((wall, t_schur, t_qdldl))
-    wall = float(np.mean([t[0] for t in times]))
-    return {"solves_per_s": sample / wall, "ms_per_step": wall * 1e3,
-            "schur_share": float(np.mean([t[1] / (t[1] + t[2]) for t in times]))}
+            walls.append(wall)
+    wall = float(np.mean(walls))
+    sample = min(B, max(threads * 16, 256))
+    ws = []
+    for it in range(3):
+        _, w2, t_schur, t_qdldl = pool.kkt(d["G"][:sample], d["C"][:sample], d["g"][:sample], d["c"][:sample], d["rho"])
+        if it >= 1:
+            ws.append((w2, t_schur / (t_schur + t_qdldl)))
+    pool.close()
+    out = {"solves_per_s": B / wall, "ms_per_step": wall * 1e3, "batch": B,
+           "with_schur": {"solves_per_s": sample / float(np.mean([w[0] for w in ws])), "sample": sample,
+                          "restatement_share": float(np.mean([w[1] for w in ws]))}}
+    if keep:
+        out["lam_star"] = lam          # QDLDL (float) solutions of the whole batch: the warm-start leg perturbs them
+    return out
+
+
+def cpu_baseline_object(r, threads, B):
+    return {"value": r["solves_per_s"], "unit": "solves/s", "cores": threads, "kind": "reference",
+            "sample": "all %d instances of the bench batch per step; reference QDLDL factor + solve (oracle/_ref, the "
+                      "reference's qdldl.c) on precomputed CSC values, persistent pool, elimination tree once; 100%% "
+                      "reference-authored code in the timed region" % B,
+            "qdldl_only": {"solves_per_s": r["solves_per_s"], "ms_per_step": r["ms_per_step"], "builder_code_share": 0.0},
+            "with_schur_restatement": {"solves_per_s": r["with_schur"]["solves_per_s"], "sample": r["with_schur"]["sample"],
+                                       "builder_code_share": r["with_schur"]["restatement_share"],
+                                       "note": "adds the oracle's CPU restatement of form_schur_qdl_kernel (S, gamma, G^-1; "
+                                               "no preconditioner) + CSC packing; the reference runs that stage on the GPU"}}
+
+
+def qdldl_single_core(torch, dev):
+    """SURVEY 8(d) CPU baseline (1) / BASELINE.json configs[0]: the reference's QDLDL host solve of ONE system on ONE
+    core (median of 200 repetitions after 20 warm-ups) at N = 32 / 64 / 128 / 512, and the PCIe round trip its slot
+    pays per solve (include/qdldl/sqp.cuh:268-273: blocking pageable D2H of nnz + s*N floats, H2D of s*N floats)."""
+    import oracle
+    from mpcgpu_b200 import synth
+    out = {}
+    for n in (32, 64, 128, 512):
+        d = synth.gen_kkt(n, 1, seed=synth.BASE_SEED + n)
+        S32, _, g32, _ = oracle.schur(S, C, n, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], np.float32)
+        us, _ = oracle.qdldl_single_core_us(S, n, S32, g32, reps=200, warmup=20)
+        nnz = (n - 1) * S * S + n * (S + 1) * S // 2
+        rec = {"factor_solve_us": us, "nnz": nnz}
+        if torch is not None:
+            d_val = torch.zeros(nnz, device=dev); d_g = torch.zeros(S * n, device=dev); d_l = torch.zeros(S * n, device=dev)
+            h_val = torch.zeros(nnz); h_g = torch.zeros(S * n); h_l = torch.zeros(S * n)      # pageable, like the reference's malloc
+            ts = []
+            for rep in range(220):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                h_val.copy_(d_val); h_g.copy_(d_g); d_l.copy_(h_l)
+                torch.cuda.synchronize()
+                if rep >= 20:
+                    ts.append((time.perf_counter() - t0) * 1e6)
+            rec["pcie_round_trip_us"] = float(np.median(ts))
+        out[str(n)] = rec
+    return out
 
 
 def _graph_time_us(torch, fn, reset, reps=20):
@@ -285,6 +347,46 @@ def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, reps=30):
             "exchange": "tagged 8-byte NVLink peer stores into per-GPU mailboxes, polled locally; no NCCL in the solve"}
 
 
+def parity_block(N, d, lam, it, ex, tol, samples):
+    """Instances drawn from the TIMED batch itself (their lambda / iteration counts are those of the last timed step)
+    against the oracle and the reference's QDLDL -- outside the timed region, the oracle as the checker only."""
+    from oracle import parity
+    B = lam.shape[0]
+    idx = np.linspace(0, B - 1, min(samples, B)).astype(int)
+    lam_h, it_h, ex_h = lam[idx].cpu().numpy(), it[idx].cpu().numpy(), ex[idx].cpu().numpy()
+    rows = []
+    for j, b in enumerate(idx):
+        sysd = parity.systems(N, d["G"][b], d["C"][b], d["g"][b], d["c"][b], d["rho"])
+        rows.append(parity.record(N, sysd, np.zeros(S * N, np.float32), tol, lam_h[j], int(it_h[j]), bool(ex_h[j])))
+    out = parity.summarize(rows)
+    out["instances"] = [int(b) for b in idx]
+    return out
+
+
+def warm_start_leg(torch, mg, N, B, G, G0, Cm, g, cv, rho, lam_star, it, ex, tol, steps):
+    """the reference's operating point is a warm-started lambda (include/mpcsim.cuh:227,383).  Same batch,
+    lambda0 = lambda* (1 + N(0, 1e-2)) with lambda* = the reference QDLDL solutions; kernel time by CUDA events."""
+    rng = np.random.default_rng(12345)
+    warm = (lam_star * (1.0 + 1e-2 * rng.standard_normal(lam_star.shape))).astype(np.float32)
+    lam0 = torch.from_numpy(warm).to(G.device)
+    lam = lam0.clone()
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    ts = []
+    for k in range(3 + steps):
+        G.copy_(G0); lam.copy_(lam0)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        mg.kkt_solve(S, C, N, G, Cm, g, cv, rho, lam, it, ex, cfg, batch=B)
+        e1.record(); torch.cuda.synchronize()
+        if k >= 3:
+            ts.append(e0.elapsed_time(e1))
+    ms = float(np.mean(ts))
+    iters = it.float()
+    return {"solves_per_s": B / (ms * 1e-3), "kernel_ms": ms, "mean_iters": float(iters.mean().item()),
+            "max_iters": int(iters.max().item()), "max_iter_exits": int(ex.sum().item()),
+            "lambda0": "lambda*(1 + N(0, 1e-2)), lambda* = reference QDLDL (float) on the oracle's S"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -295,6 +397,7 @@ def main():
     ap.add_argument("--knots", type=int, default=64)
     ap.add_argument("--tol", type=float, default=1e-4)
     ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--parity-samples", type=int, default=32)
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -310,17 +413,15 @@ def main():
         if rank != 0:
             return
         threads = os.cpu_count() or 1
-        sample = max(threads * 8, 256)
-        r = cpu_reference_run(N, sample, a.steps, max(a.warmup, 1), threads)
+        r = cpu_reference_run(N, B, a.steps, max(a.warmup, 1), threads)
         line = {"impl": "reference", "metric": "batched_kkt_solves_per_sec", "value": r["solves_per_s"],
                 "unit": "solves/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": config,
-                "cpu_baseline": {"value": r["solves_per_s"], "unit": "solves/s", "cores": threads, "kind": "reference",
-                                 "sample": "%d of the %d instances per step; Schur formation = oracle restatement "
-                                           "(share %.2f of CPU time), factor/solve = reference QDLDL (oracle/_ref)"
-                                           % (sample, B, r["schur_share"])},
-                "e2e": {"value": r["solves_per_s"], "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+                "cpu_baseline": cpu_baseline_object(r, threads, B),
+                "e2e": {"value": r["solves_per_s"], "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "note": "the reference's CPU work on this path is its QDLDL host solve (direct LDL^T, no iteration); its "
+                        "Schur formation runs on the GPU and is NOT in this figure -- see cpu_baseline.with_schur_restatement"}
         print(json.dumps(line))
         return
 
@@ -411,16 +512,28 @@ def main():
     h2d = 4 * B * (hG[0].numel() + hC[0].numel() + hg[0].numel() + hc[0].numel() + S * N)
     d2h = B * (4 * S * N + 4 + 1)
     hs.close()
-    # what bounds e2e: the host->device copy of the KKT blocks.  Measured pinned H2D rate of this box, same process.
+    # what bounds e2e: the host->device copy of the KKT blocks.  Measured pinned H2D rate of this box, same process:
+    # rank 0 alone, then ALL ranks copying at the same time (they share the host's PCIe root / memory).
     probe_h = torch.empty(256 << 20, dtype=torch.uint8).pin_memory()
     probe_d = torch.empty_like(probe_h, device=dev)
-    pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    probe_d.copy_(probe_h, non_blocking=True); torch.cuda.synchronize()
-    pe0.record()
-    for _ in range(4):
-        probe_d.copy_(probe_h, non_blocking=True)
-    pe1.record(); torch.cuda.synchronize()
-    h2d_gbps = 4 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+
+    def h2d_rate():
+        pe0, pe1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        probe_d.copy_(probe_h, non_blocking=True); torch.cuda.synchronize()
+        pe0.record()
+        for _ in range(4):
+            probe_d.copy_(probe_h, non_blocking=True)
+        pe1.record(); torch.cuda.synchronize()
+        return 4 * probe_h.numel() / (pe0.elapsed_time(pe1) * 1e-3) / 1e9
+
+    h2d_gbps = h2d_rate() if rank == 0 else 0.0
+    h2d_conc = h2d_gbps
+    if dist is not None:
+        barrier()
+        mine = h2d_rate()                       # every rank at once
+        tt = torch.tensor([mine], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+        h2d_conc = float(tt[0])
     del probe_h, probe_d
 
     ks = None
@@ -435,7 +548,9 @@ def main():
         mhz = (clocks or {}).get("sm_mhz") or (clocks or {}).get("sm_max_mhz") or 1965.0
         fp32_peak = props.multi_processor_count * 128 * 2 * mhz * 1e6 / 1e12      # FMA lanes x 2 flop x SM clock under load
         prof = os.path.join(ROOT, "profiles", "traffic.json")
-        traffic = json.load(open(prof)).get("fused_kernel_dram_bytes_per_launch") if os.path.exists(prof) else None
+        tj = json.load(open(prof)) if os.path.exists(prof) else {}
+        traffic = tj.get("fused_kernel_dram_bytes_per_launch")
+        ffma = tj.get("fused_kernel_fp32_flop_executed_per_launch")     # from ncu sass_thread_inst_executed (same workload)
         line = {"metric": "batched_kkt_solves_per_sec", "value": world * B / (ms_per_step * 1e-3), "unit": "solves/s",
                 "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_per_step,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -443,24 +558,33 @@ def main():
                 "pcg_iters": {"mean": float(iters.mean()), "min": int(iters.min()), "max": int(iters.max())},
                 "e2e": {"value": world * B / e2e_s, "unit": "solves/s", "h2d_bytes_per_step": int(h2d),
                         "d2h_bytes_per_step": int(d2h), "bound": "pcie_h2d", "h2d_achieved_GBps": h2d / e2e_s / 1e9,
-                        "h2d_peak_GBps": h2d_gbps, "h2d_frac": h2d / e2e_s / 1e9 / h2d_gbps,
-                        "note": "peak = pinned 256 MiB H2D copies timed in this process on rank 0 (ranks share the host's PCIe / memory at N > 1)"},
+                        "h2d_peak_GBps": h2d_conc, "h2d_frac": h2d / e2e_s / 1e9 / h2d_conc, "h2d_peak_GBps_rank0_alone": h2d_gbps,
+                        "note": "per-rank figures; peak = pinned 256 MiB H2D copies timed in this process with ALL ranks "
+                                "copying at the same time (min over ranks): the ranks share the host's PCIe / memory"},
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                             "traffic": traffic, "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs)" if how == "measured" else how,
+                             "traffic": traffic, "traffic_source": "static: " + tj.get("source", "profiles/traffic.json") if traffic else None,
+                             "peak_source": how + " (MEASURED_PEAKS.json hbm_gbs)" if how == "measured" else how,
                              "kernel": "fused_kernel (schur_rows + pcg_rows)", "kernel_ms": kern_ms,
                              "bytes_def": "Def. B 3388N-1596 B/instance (SURVEY 8d)",
                              "def_a_equiv_GBps": B * def_a_bytes(N) / (kern_ms * 1e-3) / 1e9,
                              "fp32_tflops": flops / (kern_ms * 1e-3) / 1e12,
                              "fp32_peak_tflops": fp32_peak, "fp32_frac": flops / (kern_ms * 1e-3) / 1e12 / fp32_peak,
-                             "note": "FP32/latency bound by design: arithmetic intensity >= 10 flop/B at 0 iterations; fp32_frac = achieved / (SMs x 128 FMA lanes x 2 x measured SM clock)"}}
+                             "fp32_tflops_executed": (ffma / (kern_ms * 1e-3) / 1e12) if ffma else None,
+                             "fp32_frac_executed": (ffma / (kern_ms * 1e-3) / 1e12 / fp32_peak) if ffma else None,
+                             "note": "FP32/latency bound by design: arithmetic intensity >= 10 flop/B at 0 iterations (81 flop/B at the "
+                                     "bench's 84 iterations, ridge 11 flop/B): at 100% FP32 issue the HBM fraction could reach ~14%, so "
+                                     "north_star's 60% HBM target does not apply to a fused kernel; fp32_frac = nominal flops "
+                                     "(60 kflop/knot Schur + 2520/knot/iteration) / (SMs x 128 FMA lanes x 2 x measured SM clock); "
+                                     "fp32_frac_executed = the kernel's own executed FFMA/FADD/FMUL thread instructions (ncu, static "
+                                     "capture of the same workload) over the same peak"}}
         if world == 1:
             threads = os.cpu_count() or 1
-            sample = max(threads * 8, 256)
-            r = cpu_reference_run(N, sample, 3, 1, threads)
-            line["cpu_baseline"] = {"value": r["solves_per_s"], "unit": "solves/s", "cores": threads, "kind": "reference",
-                                    "sample": "%d instances x 3 passes; oracle Schur restatement (share %.2f) + reference QDLDL"
-                                              % (sample, r["schur_share"])}
+            r = cpu_reference_run(N, B, 3, 1, threads, keep=True)
+            line["cpu_baseline"] = cpu_baseline_object(r, threads, B)
+            line["parity"] = parity_block(N, d, lam, it, ex, a.tol, a.parity_samples)
+            line["warm_start"] = warm_start_leg(torch, mg, N, B, G, G0, Cm, g, cv, rho, r["lam_star"], it, ex, a.tol, a.steps)
             if not a.no_extras:
+                line["qdldl_single_core_us"] = qdldl_single_core(torch, dev)
                 line["two_stage"] = two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, a.tol, peak)
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
                 line["f64"] = f64_leg(torch, mg, N, min(B, 1024), a.tol)

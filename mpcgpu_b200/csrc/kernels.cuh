@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_split_kernel(SplitAr
     RowsOf<CF> R;
     load_rows<CF>(smem, R, a.S + ks * 3 * 196, a.Pinv + ks * 3 * 196, a.gamma + ks * 14, a.n_local,
                   X.grank > 0, X.grank + 1 < X.world);
-    pcg_rows<CF, true>(smem, R, a.lambda + ks * 14, a.n_local, a.max_iter, a.exit_tol, a.iters + c,
+    pcg_rows<CF, true, 0>(smem, R, a.lambda + ks * 14, a.n_local, a.max_iter, a.exit_tol, a.iters + c,
                        a.exits + c, &X);
 }
 

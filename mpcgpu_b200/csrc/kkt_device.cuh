@@ -37,6 +37,13 @@ namespace mpcb200 {
 #ifndef MPCB200_PINV_TMEM
 #define MPCB200_PINV_TMEM 1   // 0: Pinv rows stay in shared memory during the PCG phase (A/B builds)
 #endif
+#ifndef MPCB200_TM_BALANCED
+#define MPCB200_TM_BALANCED 1 // 1: registers hold Sl, Sd, Pd and tensor memory Sr, Pl, Pr (each matvec streams <= 2 of its 3
+                              //    blocks from tensor memory); 0: S in registers, all of Pinv in tensor memory (round 1)
+#endif
+#ifndef MPCB200_PCG_VARIANT
+#define MPCB200_PCG_VARIANT 0 // default iteration of pcg_rows: 0 = the reference's two-reduction PCG, 1 = single-reduction PCG
+#endif
 constexpr int pow2_at_least(int x) { int p = 32; while (p < x) p *= 2; return p; }
 
 // scalar traits: T2 = the 16 B (double) / 8 B (float) pair type all pair-wise arithmetic runs on
@@ -52,6 +59,7 @@ struct Cfg {
     using T2 = typename Num<T_>::T2;
     static constexpr bool F32 = sizeof(T_) == 4;
     static constexpr bool TM = TM_ != 0 && F32;
+    static constexpr bool TMB = TM && MPCB200_TM_BALANCED != 0;
     static constexpr int S = 14, C = 7;
     static constexpr int KPC = KPC_, CL = CL_;
     static constexpr int LPK = LPK_;            // lanes per knot
@@ -121,6 +129,11 @@ __device__ __forceinline__ double2 neg2(double2 a) { return make_double2(-a.x, -
 __device__ __forceinline__ double2 fma2(double2 a, double2 b, double2 c) { return make_double2(fma(a.x, b.x, c.x), fma(a.y, b.y, c.y)); }
 __device__ __forceinline__ float fm(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double fm(double a, double b, double c) { return fma(a, b, c); }
+#ifndef MPCB200_FAST_DIV
+#define MPCB200_FAST_DIV 0    // 1 (experiment): alpha, beta by the approximate division (2 ulp) instead of the IEEE one
+#endif
+__device__ __forceinline__ float divT(float a, float b) { return MPCB200_FAST_DIV ? __fdividef(a, b) : a / b; }
+__device__ __forceinline__ double divT(double a, double b) { return a / b; }
 __device__ __forceinline__ float absT(float a) { return fabsf(a); }
 __device__ __forceinline__ double absT(double a) { return fabs(a); }
 __device__ __forceinline__ float getp(const float2 (&a)[7], int i) { return (i & 1) ? a[i >> 1].y : a[i >> 1].x; }
@@ -688,6 +701,57 @@ __device__ __forceinline__ double sum_partials(const double* r) {
     return (acc[0] + acc[1]) + (acc[2] + acc[3]);
 }
 
+// NRED (a, b) pairs at `r`, added in two interleaved chains per component in a fixed order (broadcast loads)
+template <int NRED>
+__device__ __forceinline__ float2 sum_pairs(const float2* r) {
+    float2 a0 = make_float2(0.f, 0.f), a1 = make_float2(0.f, 0.f);
+    if constexpr (NRED % 2 == 0 && NRED <= 64) {
+        const float4* r4 = reinterpret_cast<const float4*>(r);
+#pragma unroll
+        for (int q = 0; q < NRED / 2; q++) {
+            const float4 v = r4[q];
+            a0.x += v.x; a0.y += v.y; a1.x += v.z; a1.y += v.w;
+        }
+    } else if constexpr (NRED <= 64) {
+#pragma unroll
+        for (int q = 0; q < NRED; q++) { const float2 v = r[q]; if (q & 1) { a1.x += v.x; a1.y += v.y; } else { a0.x += v.x; a0.y += v.y; } }
+    } else {      // many partials: four pairs per lane, then a butterfly
+        static_assert(NRED % 4 == 0 && NRED <= 128, "four pairs per lane");
+        const int lane = threadIdx.x & 31;
+        if (lane < NRED / 4) {
+            const float4 u = reinterpret_cast<const float4*>(r)[2 * lane], v = reinterpret_cast<const float4*>(r)[2 * lane + 1];
+            a0 = make_float2((u.x + u.z) + (v.x + v.z), (u.y + u.w) + (v.y + v.w));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a0.x += __shfl_xor_sync(0xffffffffu, a0.x, o); a0.y += __shfl_xor_sync(0xffffffffu, a0.y, o); }
+    }
+    return make_float2(a0.x + a1.x, a0.y + a1.y);
+}
+template <int NRED>
+__device__ __forceinline__ double2 sum_pairs(const double2* r) {
+    double2 a0 = make_double2(0.0, 0.0), a1 = make_double2(0.0, 0.0);
+    if constexpr (NRED <= 64) {
+#pragma unroll
+        for (int q = 0; q < NRED; q++) { const double2 v = r[q]; if (q & 1) { a1.x += v.x; a1.y += v.y; } else { a0.x += v.x; a0.y += v.y; } }
+    } else {
+        static_assert(NRED % 4 == 0 && NRED <= 128, "four pairs per lane");
+        const int lane = threadIdx.x & 31;
+        if (lane < NRED / 4) {
+            const double2 p0 = r[4 * lane], p1 = r[4 * lane + 1], p2 = r[4 * lane + 2], p3 = r[4 * lane + 3];
+            a0 = make_double2((p0.x + p1.x) + (p2.x + p3.x), (p0.y + p1.y) + (p2.y + p3.y));
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a0.x += __shfl_xor_sync(0xffffffffu, a0.x, o); a0.y += __shfl_xor_sync(0xffffffffu, a0.y, o); }
+    }
+    return make_double2(a0.x + a1.x, a0.y + a1.y);
+}
+// one (a, b) pair to a peer CTA's shared memory, completing its bytes on that CTA's mbarrier
+__device__ __forceinline__ void st_async_pair(uint32_t a, float x, float y, uint32_t mb) {
+    const unsigned long long v = (unsigned long long)__float_as_uint(x) | ((unsigned long long)__float_as_uint(y) << 32);
+    asm volatile("st.async.shared::cluster.mbarrier::complete_tx::bytes.b64 [%0], %1, [%2];" ::"r"(a), "l"(v), "r"(mb) : "memory");
+}
+__device__ __forceinline__ void st_async_pair(uint32_t a, double x, double y, uint32_t mb) { st_async_f64(a, x, mb); st_async_f64(a + 8u, y, mb); }
+
 template <class CF>
 __device__ __forceinline__ typename CF::T cluster_sum(typename CF::T* red, uint64_t* mb, unsigned (&par)[2], int buf,
                                                       typename CF::T val, unsigned rank, unsigned halo_bytes) {
@@ -763,7 +827,7 @@ __device__ __forceinline__ float sys_poll_tagged(const uint2* src, unsigned tag)
 // along with the partial sums, so neighbouring CTAs update their halo copies of r and p
 // locally and need no further exchange.
 // ---------------------------------------------------------------------------------------
-template <class CF, bool SPLIT = false>
+template <class CF, bool SPLIT = false, int VAR = MPCB200_PCG_VARIANT>
 __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>& R, typename CF::T* lam_g, int N,
                                          unsigned max_iter, typename CF::T exit_tol, unsigned* d_iters,
                                          uint8_t* d_exit, const SplitCtx* X = nullptr) {
@@ -804,8 +868,69 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         tmem_fence_before_sync();
     }
 
+    // Balanced operand stores (TMB): registers hold Sl, Sd (R) and Pd (below), tensor memory holds Sr | Pl | Pr as
+    // 7 chunks of 2*RPT columns (column pair w of my RPT rows of Sr) followed by 7 chunks of 4*RPT (Pl pair w |
+    // Pr pair w).  The tensor-memory read path delivers ~1/4 of what the FFMA2 pipe can consume, so a matvec that
+    // streams all three of its blocks from it (round 1: Pinv) is bound by that path, and one that streams none
+    // leaves it idle; with one block of S and two of Pinv there, both matvecs sit near the FFMA2 floor.  Every
+    // accumulation chain keeps its order, so the bits are those of the all-register / all-TMEM forms.
+    constexpr bool TMB = CF::TMB;
+    T2 Pd[TMB ? RPT : 1][7];
+    auto s_mv_tm = [&](const T* vec, T (&y)[RPT]) {
+      if constexpr (TMB) {
+        TmemChunk<2 * RPT> buf[2];
+        buf[0].ld(tcol);
+        const T2* vl = reinterpret_cast<const T2*>(vec + (sl - 1) * VK);
+        const T2* vd = reinterpret_cast<const T2*>(vec + sl * VK);
+        const T2* vr = reinterpret_cast<const T2*>(vec + (sl + 1) * VK);
+        T2 al[RPT], ad[RPT], ar[RPT];
+#pragma unroll
+        for (int j = 0; j < RPT; j++) { al[j] = splat(T(0)); ad[j] = splat(T(0)); ar[j] = splat(T(0)); }
+#pragma unroll
+        for (int w = 0; w < 7; w++) {
+            const T2 xl = vl[w], xd = vd[w], xr = vr[w];
+#pragma unroll
+            for (int j = 0; j < RPT; j++) { al[j] = fma2(R.Sl[j][w], xl, al[j]); ad[j] = fma2(R.Sd[j][w], xd, ad[j]); }
+            buf[w & 1].wait();          // tcgen05.wait::ld covers every load in flight: wait, THEN start the next
+            if (w + 1 < 7) buf[(w + 1) & 1].ld(tcol + (w + 1) * 2 * RPT);
+#pragma unroll
+            for (int j = 0; j < RPT; j++)
+                ar[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * j]), __uint_as_float(buf[w & 1].q[2 * j + 1])), xr, ar[j]);
+        }
+#pragma unroll
+        for (int j = 0; j < RPT; j++) y[j] = (hsum(al[j]) + hsum(ad[j])) + hsum(ar[j]);
+      }
+    };
+    auto p_mv_tmb = [&](const T* vec, T (&y)[RPT]) {
+      if constexpr (TMB) {
+        TmemChunk<4 * RPT> buf[2];
+        const uint32_t base = tcol + 7 * 2 * RPT;
+        buf[0].ld(base);
+        const T2* vl = reinterpret_cast<const T2*>(vec + (sl - 1) * VK);
+        const T2* vd = reinterpret_cast<const T2*>(vec + sl * VK);
+        const T2* vr = reinterpret_cast<const T2*>(vec + (sl + 1) * VK);
+        T2 a0[RPT], a1[RPT], a2[RPT];
+#pragma unroll
+        for (int j = 0; j < RPT; j++) { a0[j] = splat(T(0)); a1[j] = splat(T(0)); a2[j] = splat(T(0)); }
+#pragma unroll
+        for (int w = 0; w < 7; w++) {
+            const T2 xl = vl[w], xd = vd[w], xr = vr[w];
+#pragma unroll
+            for (int j = 0; j < RPT; j++) a0[j] = fma2(Pd[j][w], xd, a0[j]);
+            buf[w & 1].wait();
+            if (w + 1 < 7) buf[(w + 1) & 1].ld(base + (w + 1) * 4 * RPT);
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                a1[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * j]), __uint_as_float(buf[w & 1].q[2 * j + 1])), xl, a1[j]);
+                a2[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * RPT + 2 * j]), __uint_as_float(buf[w & 1].q[2 * RPT + 2 * j + 1])), xr, a2[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RPT; j++) y[j] = rm.ok[j] ? (hsum(a1[j]) + hsum(a0[j])) + hsum(a2[j]) : T(0);
+      }
+    };
     // y(rows) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
-    auto s_mv = [&](const T* vec, T (&y)[RPT]) {
+    auto s_mv_reg = [&](const T* vec, T (&y)[RPT]) {
         T2 xl[7], xd[7], xr[7];
         ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
 #pragma unroll
@@ -886,7 +1011,10 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         }
       }
     };
-    auto pinv_mv = [&](const T* vec, T (&y)[RPT]) { if constexpr (TM) p_mv_tm(vec, y); else p_mv(vec, y); };
+    auto pinv_mv = [&](const T* vec, T (&y)[RPT]) {
+        if constexpr (TMB) p_mv_tmb(vec, y); else if constexpr (TM) p_mv_tm(vec, y); else p_mv(vec, y);
+    };
+    auto s_mv = [&](const T* vec, T (&y)[RPT]) { if constexpr (TMB) s_mv_tm(vec, y); else s_mv_reg(vec, y); };
     auto put = [&](T* dst, const T (&v)[RPT]) {        // my rows of a 16-T vector slot
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) dst[rm.row[j]] = v[j];
@@ -960,6 +1088,28 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         gpull_rows(2, tg0, hl_p, hr_p);
     }
     __syncthreads();
+    if constexpr (TMB) {   // my PROW rows are final (schur_rows / load_rows ended on a barrier): Sr, Pl, Pr -> tensor memory, Pd -> registers
+        tmem_fence_after_sync();
+        const int warp = tid >> 5;
+        tcol = *tm_word + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * CF::TPT);
+#pragma unroll
+        for (int w = 0; w < 7; w++) {
+            TmemChunk<2 * RPT> cs;
+            TmemChunk<4 * RPT> cp;
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                const T2 pl = *reinterpret_cast<const T2*>(myP + rm.row[j] * PR + CF::cL + 2 * w);
+                const T2 pr = *reinterpret_cast<const T2*>(myP + rm.row[j] * PR + CF::cR + 2 * w);
+                Pd[j][w] = *reinterpret_cast<const T2*>(myP + rm.row[j] * PR + CF::cD + 2 * w);
+                cs.q[2 * j] = __float_as_uint(R.Sr[j][w].x); cs.q[2 * j + 1] = __float_as_uint(R.Sr[j][w].y);
+                cp.q[2 * j] = __float_as_uint(pl.x); cp.q[2 * j + 1] = __float_as_uint(pl.y);
+                cp.q[2 * RPT + 2 * j] = __float_as_uint(pr.x); cp.q[2 * RPT + 2 * j + 1] = __float_as_uint(pr.y);
+            }
+            cs.st(tcol + w * 2 * RPT);
+            cp.st(tcol + 7 * 2 * RPT + w * 4 * RPT);
+        }
+        tmem_wait_st();
+    }
     s_mv(pv, y);
 #pragma unroll
     for (int j = 0; j < RPT; j++) rr[j] = rm.ok[j] ? R.gamma[j] - y[j] : T(0);
@@ -969,7 +1119,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     if (SPLIT) gpull_rows(3, tg0, hl_r, hr_r);
     cluster_sync_all<CL>();
 
-    if constexpr (TM) {   // PROW is final (barrier above): move my Pinv rows into tensor memory
+    if constexpr (TM && !TMB) {   // PROW is final (barrier above): move my Pinv rows into tensor memory
         tmem_fence_after_sync();
         const int warp = tid >> 5;
         tcol = *tm_word + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * CF::TPT);
@@ -991,6 +1141,92 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         }
         tmem_wait_st();
     }
+    unsigned iter = 0;
+    bool max_iter_exit = true;
+    if constexpr (VAR == 1) {
+    // ---- single-reduction PCG (Chronopoulos & Gear): u = Pinv r, w = S u, ONE reduction of the pair
+    // (r.u, u.w) per iteration; p.Sp = u.w - beta^2 (p.Sp)_old; q = S p by recurrence.  Same Krylov
+    // iterates as the loop below in exact arithmetic, same exit test / iteration count / flag
+    // (checked against oracle_pcg_cg1).  Per iteration: 3 CTA barriers, one shuffle tree.
+    static_assert(!SPLIT, "the knot-range split runs the two-reduction iteration");
+    T* hw = hal;               // [side][VK] boundary rows of S u pushed by the neighbour CTAs (side 0: my LEFT one)
+    T* hq = hal + 2 * VK;      // [side][VK] q rows of the neighbours' boundary knots, by the same recurrence
+    T2* red2 = reinterpret_cast<T2*>(red);
+    if (CL > 1) { if (first_g) put(hq, zero); if (last_g) put(hq + VK, zero); }
+    T qq[RPT];
+#pragma unroll
+    for (int j = 0; j < RPT; j++) { pp[j] = T(0); qq[j] = T(0); }
+    // rt = Pinv r -> published in pv (own rows + the neighbour CTAs' halo slots) ; y = S rt
+    auto mv_pair = [&]() {
+        pinv_mv(rv, rt);
+        put(pv + sl * VK, rt);
+        if constexpr (CL > 1) {
+            if (tid == 0) mbar_arrive_expect_tx(mb + 0, hb);
+            if (first_g && has_l) push(hr_p, rank - 1, 0, rt);
+            if (last_g && has_r)  push(hl_p, rank + 1, 0, rt);
+            __syncthreads();
+            mbar_wait(mb + 0, par[0]);
+            par[0] ^= 1u;
+        } else {
+            __syncthreads();
+        }
+        s_mv(pv, y);
+    };
+    // cluster-wide sums of (a, b), bit-identical in every thread; the boundary rows of y travel with them
+    auto sum2 = [&](T a, T b) -> T2 {
+        const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); }
+        T2* slot = red2 + rank * CF::NW + warp;
+        if constexpr (CL == 1) {
+            if (lane == 0) *slot = f2(a, b);
+            __syncthreads();
+        } else {
+            if (tid == 0) mbar_arrive_expect_tx(mb + 1, (unsigned)CF::NRED * (unsigned)sizeof(T2) + hb);
+            if (lane < CL) st_async_pair(mapa_u32(smem_u32(slot), (unsigned)lane), a, b, mapa_u32(smem_u32(mb + 1), (unsigned)lane));
+            if (first_g && has_l) push(hw + 1 * VK, rank - 1, 1, y);
+            if (last_g && has_r)  push(hw + 0 * VK, rank + 1, 1, y);
+            mbar_wait(mb + 1, par[1]);
+            par[1] ^= 1u;
+        }
+        return sum_pairs<CF::NRED>(red2);
+    };
+    if (first_g && !has_l) put(hl_p, zero);
+    if (last_g && !has_r)  put(hr_p, zero);
+    mv_pair();
+    T2 gd = sum2(dotp(rr, rt), dotp(rt, y));
+    T gam_old = T(1), c_old = T(0);
+    for (; iter < max_iter; iter++) {
+        const T gam = gd.x;
+        const T v = fm(-(gam * gam), c_old, gd.y);          // p.Sp
+        if (v == T(0)) { max_iter_exit = false; break; }
+        const T alpha = gam / v;
+        const T beta = iter ? gam / gam_old : T(0);
+#pragma unroll
+        for (int j = 0; j < RPT; j++) {
+            pp[j] = fm(beta, pp[j], rt[j]);
+            qq[j] = fm(beta, qq[j], y[j]);
+            lam[j] = fm(alpha, pp[j], lam[j]);
+            rr[j] = fm(-alpha, qq[j], rr[j]);
+        }
+        put(rv + sl * VK, rr);
+        if (CL > 1) {       // the neighbours' boundary knots: the same recurrences on the pushed rows of S u
+#pragma unroll
+            for (int j = 0; j < RPT; j++) {
+                if (!rm.ok[j]) continue;
+                const int r = rm.row[j];
+                if (first_g && has_l) { const T q = fm(beta, hq[r], hw[r]); hq[r] = q; hl_r[r] = fm(-alpha, q, hl_r[r]); }
+                if (last_g && has_r)  { const T q = fm(beta, hq[VK + r], hw[VK + r]); hq[VK + r] = q; hr_r[r] = fm(-alpha, q, hr_r[r]); }
+            }
+        }
+        c_old = (v / gam) / gam;     // off the critical path: needed after the next reduction
+        gam_old = gam;
+        __syncthreads();
+        mv_pair();
+        gd = sum2(dotp(rr, rt), dotp(rt, y));
+        if (absT(gd.x) < exit_tol) { iter++; max_iter_exit = false; break; }
+    }
+    } else {
     // ---- p = rt = Pinv r ; eta = r.rt ----------------------------------------------------------
     pinv_mv(rv, rt);
 #pragma unroll
@@ -1002,8 +1238,6 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     T eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
     if (SPLIT) { eta = gsum(1, ++gseq[1], eta); __syncthreads(); }
 
-    unsigned iter = 0;
-    bool max_iter_exit = true;
     for (; iter < max_iter; iter++) {
         // ---- ups = S p ; v = p.ups -----------------------------------------------------------
         s_mv(pv, y);
@@ -1018,7 +1252,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         T v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
         if (SPLIT) v = gsum(0, ++gseq[0], v);
         if (v == T(0)) { max_iter_exit = false; break; }
-        const T alpha = eta / v;
+        const T alpha = divT(eta, v);
 #pragma unroll
         for (int j = 0; j < RPT; j++) { lam[j] = fm(alpha, pp[j], lam[j]); rr[j] = fm(-alpha, y[j], rr[j]); }
         put(rv + sl * VK, rr);
@@ -1054,7 +1288,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         T eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
         if (SPLIT) eta_new = gsum(1, ++gseq[1], eta_new);
         if (absT(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
-        const T beta = eta_new / eta;
+        const T beta = divT(eta_new, eta);
         eta = eta_new;
 #pragma unroll
         for (int j = 0; j < RPT; j++) pp[j] = fm(beta, pp[j], rt[j]);
@@ -1079,6 +1313,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         }
         __syncthreads();
     }
+    }   // VAR
 #pragma unroll
     for (int j = 0; j < RPT; j++) if (valid && rm.ok[j]) lam_g[(size_t)k * S + rm.row[j]] = lam[j];
     if (rank == 0 && tid == 0) { *d_iters = iter; *d_exit = max_iter_exit ? 1 : 0; }

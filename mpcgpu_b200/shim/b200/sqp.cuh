@@ -101,8 +101,10 @@ struct Workspace {
     cudaGraphExec_t exec = nullptr;
     bool graph_failed = false;
     const void* key_ptr[4] = {nullptr, nullptr, nullptr, nullptr};
-    float key_dt = 0.f, key_tol = 0.f;
+    float key_dt = 0.f;
+    T key_tol = T(0);            // as T: a double tolerance (REMOVE_JITTERS sets 1e-11) must compare equal to itself
     uint32_t key_iter = 0;
+    int device = -1;             // the device the pool lives on
     Host* h = nullptr;
     cudaStream_t ls_stream[kAlphas] = {};
     uint32_t nz = 0;             // length of xu / dz
@@ -112,6 +114,7 @@ struct Workspace {
     void build(uint32_t s_, uint32_t c_, uint32_t N_) {
         release();
         s = s_; c = c_; N = N_;
+        gpuErrchk(cudaGetDevice(&device));
         nz = (s + c) * N - c;
         const size_t nG = size_t(s * s + c * c) * N - c * c, nC = size_t(s * s + s * c) * (N - 1),
                      ng = nz, nc = size_t(s) * N;
@@ -151,10 +154,15 @@ struct Workspace {
     ~Workspace() { /* process-lifetime object: the driver reclaims the memory at exit */ }
 };
 
+// One workspace per process, rebuilt when the problem size or the current device changes.  Like the reference's
+// slots (one host thread, legacy stream: SURVEY 8b "Threading / streams") it is NOT thread-safe: call
+// sqpSolveB200 from one host thread at a time.
 template <typename T>
 inline Workspace<T>& workspace(uint32_t s, uint32_t c, uint32_t N) {
     static Workspace<T> w;
-    if (w.s != s || w.c != c || w.N != N || !w.d_pool) w.build(s, c, N);
+    int dev = -1;
+    gpuErrchk(cudaGetDevice(&dev));
+    if (w.s != s || w.c != c || w.N != N || !w.d_pool || w.device != dev) w.build(s, c, N);
     return w;
 }
 
@@ -210,6 +218,13 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
     T merit_now = 0, drho = 1;
     const T rho_factor = RHO_FACTOR, rho_max = RHO_MAX, rho_min = RHO_MIN;
 
+    // MPCGPU_B200_SLOT_MAX_SQP=n caps the SQP iterations of a call below SQP_MAX_ITER (closed-loop experiments:
+    // the b200 slot with the iteration count the reference's PCG slot reaches in the same budget)
+    static const uint32_t sqp_cap = [] {
+        const char* e = getenv("MPCGPU_B200_SLOT_MAX_SQP");
+        const long v = e ? atol(e) : 0;
+        return (v > 0 && v < (long)SQP_MAX_ITER) ? (uint32_t)v : (uint32_t)SQP_MAX_ITER;
+    }();
     // ---- graph path: one captured SQP iteration, replayed ---------------------------------------
     static const bool want_graph = [] { const char* e = getenv("MPCGPU_B200_SLOT_GRAPH"); return !(e && e[0] == '0'); }();
     bool use_graph = want_graph && !fine && !time_linsys && !w.graph_failed;
@@ -258,7 +273,7 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
     if (use_graph) {
         T pending = 0;                       // accepted step, applied by the next replay (or after the loop)
         double iter_us = 0.0;                // duration of the last replay: do not start one that cannot finish
-        for (uint32_t it = 0; it < SQP_MAX_ITER; it++) {
+        for (uint32_t it = 0; it < sqp_cap; it++) {
 #if CONST_UPDATE_FREQ
             clock_gettime(CLOCK_MONOTONIC, &t_now);
             if (us_between(t_begin, t_now) + iter_us > SQP_MAX_TIME_US) break;
@@ -296,7 +311,7 @@ auto sqpSolveB200(const uint32_t state_size, const uint32_t control_size, const 
         }
     }
 
-    for (uint32_t it = 0; !use_graph && it < SQP_MAX_ITER; it++) {
+    for (uint32_t it = 0; !use_graph && it < sqp_cap; it++) {
         // 1. linearise: G, C, g, c
         lap_begin(fine);
         generate_kkt_submatrices<T><<<knot_points, KKT_THREADS, kkt_smem>>>(state_size, control_size, knot_points, w.G,

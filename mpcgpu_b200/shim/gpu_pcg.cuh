@@ -15,10 +15,19 @@
 // the caller's N CTAs stay co-resident at one 124 KB CTA per SM (N <= 64).
 // Horizons that do not fit one cluster (N > 256, or N without a usable divisor; N > 64 for double)
 // fall back to the cooperative one-CTA-per-knot kernel (csrc/refstyle_pcg.cuh).
+//
+// Stage 1 behind the same unchanged include/pcg/sqp.cuh: this header also provides the explicit specialisations
+// form_schur_system<float> / <double> of the reference's launcher template (include/pcg/linsys_setup.cuh:620-633,
+// called at include/pcg/sqp.cuh:243), so the call site binds to the sm_100a cluster kernel
+// mpcb200::schur_kernel (csrc/kernels.cuh) instead of the reference's cooperative one-CTA-per-knot
+// form_S_gamma_Pinv_kernel -- whichever of the two headers is included first.  The reference's kernel stays
+// reachable as its own template for any other type, or for every type with
+// -DMPCGPU_B200_SHIM_KEEP_REFERENCE_SCHUR (the parity harness compares the two).
 #pragma once
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <cuda_runtime.h>
 #include <type_traits>
 
@@ -136,3 +145,99 @@ bool checkPcgOccupancy(void* kernel, unsigned block, uint32_t state_size, uint32
     }
     return true;
 }
+
+
+// ---- stage 1: form_schur_system behind the unchanged call site (include/pcg/sqp.cuh:243) ---------------------
+// the reference's launcher template (include/pcg/linsys_setup.cuh:620-633), declared here so that the
+// specialisations below are valid whether or not that header has been seen yet
+template <typename T>
+void form_schur_system(uint32_t state_size, uint32_t control_size, uint32_t knot_points, T* d_G_dense, T* d_C_dense,
+                       T* d_g, T* d_c, T* d_S, T* d_Pinv, T* d_gamma, T rho);
+
+namespace mpcb200_shim {
+
+// our own launch (cluster of ceil(N / 16) CTAs, 16 knots x 8 lanes each; N = 512: 32 knots per CTA), any N
+template <typename T, uint32_t N>
+struct SchurTiling {
+    static constexpr bool F32 = std::is_same<T, float>::value;
+    static constexpr uint32_t K = (F32 && N > 256) ? 32 : KPC;
+    static constexpr uint32_t CL = (N + K - 1) / K;
+    static constexpr bool OK = CL >= 1 && CL <= 16 && (F32 || std::is_same<T, double>::value);
+    using CF = mpcb200::Cfg<(int)K, OK ? (int)CL : 1, 8, 0, T>;
+};
+
+// form_schur_system<T> for a compile-time horizon: writes d_S, d_Pinv, d_gamma, d_G_dense becomes G^-1.  Legacy
+// default stream, like the reference's launch (include/pcg/linsys_setup.cuh:656).
+template <typename T, uint32_t N>
+void form_schur_system_n(T* d_G_dense, T* d_C_dense, T* d_g, T* d_c, T* d_S, T* d_Pinv, T* d_gamma, T rho) {
+    using TL = SchurTiling<T, N>;
+    static_assert(TL::OK, "mpcgpu_b200 shim: form_schur_system supports KNOT_POINTS <= 512 (float) / <= 256 (double)");
+    using CF = typename TL::CF;
+    auto kern = mpcb200::schur_kernel<CF>;
+    static int configured_dev = -1;
+    int dev = 0;
+    gpuErrchk(cudaGetDevice(&dev));
+    if (configured_dev != dev) {
+        gpuErrchk(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CF::SMEM_BYTES));
+        if (CF::CL > 8) gpuErrchk(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        configured_dev = dev;
+    }
+    constexpr uint32_t s = 14, c = 7;
+    mpcb200::BatchArgsT<T> a;
+    memset(&a, 0, sizeof(a));
+    a.N = (int)N; a.batch = 1;
+    a.sG = (size_t)(s * s + c * c) * N - c * c; a.sC = (size_t)(s * s + s * c) * (N - 1);
+    a.sg = (size_t)(s + c) * N - c; a.sc = (size_t)s * N; a.sS = (size_t)3 * s * s * N; a.sv = (size_t)s * N;
+    a.G = d_G_dense; a.C = d_C_dense; a.g = d_g; a.c = d_c; a.rho = rho;
+    a.S = d_S; a.Pinv = d_Pinv; a.gamma = d_gamma;
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(CF::CL, 1, 1);
+    cfg.blockDim = dim3(CF::NT, 1, 1);
+    cfg.dynamicSmemBytes = CF::SMEM_BYTES;
+    cfg.stream = 0;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CF::CL; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    gpuErrchk(cudaLaunchKernelEx(&cfg, kern, a));
+}
+
+#if MPCB200_SHIM_HAVE_DIMS
+// the run-time signature of the reference, for the horizon this translation unit was compiled for
+template <typename T>
+void form_schur_system(uint32_t state_size, uint32_t control_size, uint32_t knot_points, T* d_G_dense, T* d_C_dense,
+                       T* d_g, T* d_c, T* d_S, T* d_Pinv, T* d_gamma, T rho) {
+    if (state_size != 14 || control_size != 7 || knot_points != KNOT_POINTS) {   // loud, never a silent fallback
+        fprintf(stderr, "mpcgpu_b200 shim: form_schur_system compiled for state 14 / control 7 / KNOT_POINTS %d, called with "
+                        "%u / %u / %u (build with -DMPCGPU_B200_SHIM_KEEP_REFERENCE_SCHUR for the reference's kernel)\n",
+                (int)KNOT_POINTS, state_size, control_size, knot_points);
+        exit(7);
+    }
+    form_schur_system_n<T, KNOT_POINTS>(d_G_dense, d_C_dense, d_g, d_c, d_S, d_Pinv, d_gamma, rho);
+}
+#endif
+
+}  // namespace mpcb200_shim
+
+#if MPCB200_SHIM_HAVE_DIMS && !defined(MPCGPU_B200_SHIM_KEEP_REFERENCE_SCHUR)
+#if KNOT_POINTS <= 512
+template <>
+inline void form_schur_system<float>(uint32_t state_size, uint32_t control_size, uint32_t knot_points, float* d_G_dense,
+                                     float* d_C_dense, float* d_g, float* d_c, float* d_S, float* d_Pinv, float* d_gamma,
+                                     float rho) {
+    mpcb200_shim::form_schur_system<float>(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, d_c, d_S, d_Pinv,
+                                           d_gamma, rho);
+}
+#endif
+#if KNOT_POINTS <= 256
+template <>
+inline void form_schur_system<double>(uint32_t state_size, uint32_t control_size, uint32_t knot_points, double* d_G_dense,
+                                      double* d_C_dense, double* d_g, double* d_c, double* d_S, double* d_Pinv,
+                                      double* d_gamma, double rho) {
+    mpcb200_shim::form_schur_system<double>(state_size, control_size, knot_points, d_G_dense, d_C_dense, d_g, d_c, d_S, d_Pinv,
+                                            d_gamma, rho);
+}
+#endif
+#endif

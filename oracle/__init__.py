@@ -110,6 +110,23 @@ def pcg(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32, mod
     return lam, int(iters.value), bool(flag.value)
 
 
+def pcg_cg1(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32):
+    """Single-reduction PCG (oracle_pcg_cg1): the checker of the product's PCG variant 1.
+    Returns (lambda, iters, max_iter_exit)."""
+    suf, ct = _dt(dtype)
+    S = np.ascontiguousarray(S, dtype=dtype)
+    Pinv = np.ascontiguousarray(Pinv, dtype=dtype)
+    gamma = np.ascontiguousarray(gamma, dtype=dtype)
+    lam = np.array(lambda0, dtype=dtype, copy=True)
+    iters = ctypes.c_uint(0)
+    flag = ctypes.c_ubyte(0)
+    fn = getattr(_lib("oracle"), "oracle_pcg_cg1_" + suf)
+    fn.restype = None
+    fn(ctypes.c_int(s), ctypes.c_int(N), _p(S), _p(Pinv), _p(gamma), _p(lam),
+       ctypes.c_uint(max_iter), ct(exit_tol), ctypes.byref(iters), ctypes.byref(flag))
+    return lam, int(iters.value), bool(flag.value)
+
+
 def pcg_noise_floor(s, N, S32, P32, g32, lambda0, iters):
     """How far correct fp32 implementations of the SAME `iters` PCG iterations drift apart on
     this input: max of (plain-order fp32 vs alternate-order fp32) and (fp32 vs fp64), relative
@@ -230,3 +247,91 @@ def cpu_kkt_solve_batch(s, c, N, G, C, g, cvec, rho, nthreads, with_schur=True, 
     if wall < 0:
         raise RuntimeError("cpu_kkt_solve_batch failed: %r" % wall)
     return lam, float(wall), float(a.value), float(b.value)
+
+
+class CpuPool:
+    """Persistent host thread pool around the REFERENCE's QDLDL (oracle/_ref/libcpu_baseline.so): threads,
+    QDLDL workspaces, CSC pattern and elimination tree live as long as the object (the reference computes
+    the tree once, include/qdldl/sqp.cuh:193)."""
+
+    def __init__(self, s, c, N, nthreads):
+        self.lib = _lib("cpu_baseline")
+        self.s, self.c, self.N, self.nthreads = s, c, N, int(nthreads)
+        self.lib.cpu_pool_create.restype = ctypes.c_void_p
+        self.lib.cpu_pool_qdldl.restype = ctypes.c_double
+        self.lib.cpu_pool_kkt.restype = ctypes.c_double
+        self.lib.cpu_pool_destroy.restype = None
+        self.h = ctypes.c_void_p(self.lib.cpu_pool_create(ctypes.c_int(s), ctypes.c_int(c), ctypes.c_int(N),
+                                                          ctypes.c_int(self.nthreads)))
+        if not self.h:
+            raise RuntimeError("cpu_pool_create failed")
+        self.nnz = sizes(s, c, N)["nnz"]
+
+    def qdldl(self, val, gamma):
+        """qdldl_solve_schur (include/qdldl/sqp.cuh:22-49) of every system given as CSC values val[batch, nnz]
+        and gamma[batch, s*N].  Returns (lambda, wall_s)."""
+        val = np.ascontiguousarray(val, np.float32)
+        gamma = np.ascontiguousarray(gamma, np.float32)
+        batch = val.size // self.nnz
+        lam = np.zeros((batch, self.s * self.N), np.float32)
+        wall = self.lib.cpu_pool_qdldl(self.h, ctypes.c_int(batch), _p(val), _p(gamma), _p(lam))
+        if wall < 0:
+            raise RuntimeError("cpu_pool_qdldl failed: %r" % wall)
+        return lam, float(wall)
+
+    def kkt(self, G, C, g, cvec, rho):
+        """Schur restatement without preconditioner (include/qdldl/linsys_setup.cuh:12-336) + CSC packing +
+        reference QDLDL.  Returns (lambda, wall_s, sum_schur_s, sum_qdldl_s)."""
+        f32 = np.float32
+        G = np.ascontiguousarray(G, f32)
+        batch = G.size // sizes(self.s, self.c, self.N)["G"]
+        lam = np.zeros((batch, self.s * self.N), f32)
+        a, b = ctypes.c_double(0), ctypes.c_double(0)
+        wall = self.lib.cpu_pool_kkt(self.h, ctypes.c_int(batch), _p(G), _p(np.ascontiguousarray(C, f32)),
+                                     _p(np.ascontiguousarray(g, f32)), _p(np.ascontiguousarray(cvec, f32)),
+                                     ctypes.c_float(rho), _p(lam), ctypes.byref(a), ctypes.byref(b))
+        if wall < 0:
+            raise RuntimeError("cpu_pool_kkt failed: %r" % wall)
+        return lam, float(wall), float(a.value), float(b.value)
+
+    def schur_csc(self, G, C, g, cvec, rho):
+        """Preparation of :meth:`qdldl`'s inputs (what the reference's GPU Schur kernel hands to the host):
+        returns (val[batch, nnz], gamma[batch, s*N])."""
+        f32 = np.float32
+        G = np.ascontiguousarray(G, f32)
+        batch = G.size // sizes(self.s, self.c, self.N)["G"]
+        val = np.zeros((batch, self.nnz), f32)
+        gam = np.zeros((batch, self.s * self.N), f32)
+        self.lib.cpu_pool_schur_csc.restype = ctypes.c_double
+        wall = self.lib.cpu_pool_schur_csc(self.h, ctypes.c_int(batch), _p(G), _p(np.ascontiguousarray(C, f32)),
+                                           _p(np.ascontiguousarray(g, f32)), _p(np.ascontiguousarray(cvec, f32)),
+                                           ctypes.c_float(rho), _p(val), _p(gam))
+        if wall < 0:
+            raise RuntimeError("cpu_pool_schur_csc failed: %r" % wall)
+        return val, gam
+
+    def close(self):
+        if self.h:
+            self.lib.cpu_pool_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def qdldl_single_core_us(s, N, S, gamma, reps=200, warmup=20):
+    """Median single-core microseconds of the reference's host solve of ONE system (QDLDL_factor + copy +
+    QDLDL_solve on precomputed CSC values, float build; include/qdldl/sqp.cuh:22-49)."""
+    lib = _lib("cpu_baseline")
+    val = csc_values(s, N, np.ascontiguousarray(S, np.float32))
+    gamma = np.ascontiguousarray(gamma, np.float32)
+    lam = np.zeros(s * N, np.float32)
+    lib.cpu_qdldl_single_us.restype = ctypes.c_double
+    us = lib.cpu_qdldl_single_us(ctypes.c_int(s), ctypes.c_int(N), _p(val), _p(gamma), ctypes.c_int(reps),
+                                 ctypes.c_int(warmup), _p(lam))
+    if us < 0:
+        raise RuntimeError("cpu_qdldl_single_us failed: %r" % us)
+    return float(us), lam

@@ -41,6 +41,7 @@ TRACK_KNOTS = (32, 128)
 SQPB = os.path.join(RUN, "sqp_batched_check")   # tools/sqp_batched_check.cu
 KKTB = os.path.join(RUN, "kkt_batched_check")   # tools/kkt_batched_check.cu
 SLOT = os.path.join(RUN, "track_slot_%s_n%d")    # tools/track_slot.cu: simulateMPC over the pcg / b200 slot
+SLOTAB = os.path.join(RUN, "slot_ab_n%d")        # tools/slot_ab.cu: one SQP iteration of either slot on identical state
 
 
 def _ref_nvcc(src, out, defs=(), link_product=False):
@@ -87,11 +88,19 @@ def _build_reference_cuda(force, verbose):
                         os.path.join(root, "include", "mpcgpu_b200.h")]
     lib = os.path.join(root, "mpcgpu_b200", "libmpcgpu_b200.so")
     for n in TRACK_KNOTS:
-        for name, flag in (("pcg", 0), ("b200", 1)):
+        # pcg: the reference's slot on the whole L1 shim (our Schur + our PCG kernels); pcgrefschur: the same with the
+        # reference's own form_schur_system kernel kept (the round-1 baseline); b200: the L2 slot
+        for name, defs in (("pcg", ["-DSLOT_B200=0"]), ("pcgrefschur", ["-DSLOT_B200=0", "-DMPCGPU_B200_SHIM_KEEP_REFERENCE_SCHUR=1"]),
+                           ("b200", ["-DSLOT_B200=1"])):
+            flag = name == "b200"
             if flag and not os.path.exists(lib):
                 continue   # product library not built yet (mpcgpu_b200.build runs first in __graft_entry__.build)
             if force or _stale(SLOT % (name, n), slot_deps):
-                jobs.append((slot_src, SLOT % (name, n), ["-DKNOT_POINTS=%d" % n, "-DSLOT_B200=%d" % flag], bool(flag)))
+                jobs.append((slot_src, SLOT % (name, n), ["-DKNOT_POINTS=%d" % n] + defs, flag))
+    ab_src = os.path.join(root, "tools", "slot_ab.cu")
+    for n in TRACK_KNOTS:
+        if os.path.exists(lib) and (force or _stale(SLOTAB % n, slot_deps + [ab_src])):
+            jobs.append((ab_src, SLOTAB % n, ["-DKNOT_POINTS=%d" % n, "-DSQP_MAX_TIME_US=100000000"], True))
     kb_src = os.path.join(root, "tools", "kkt_batched_check.cu")     # batched KKT producer vs the reference kernel
     kb_deps = deps + [kb_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "kkt_batched.cuh"),
                       os.path.join(root, "include", "mpcgpu_b200.h")]

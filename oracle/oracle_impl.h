@@ -103,6 +103,9 @@ static REAL *F(bd)(REAL *buf, int s, int block_row, int block_col)
  *   S, Pinv : 3*s*s*N ; gamma : s*N
  * Corner blocks S[0][0], S[N-1][2], Pinv[0][0], Pinv[N-1][2] are never written by
  * the reference; the oracle zero-fills them.
+ * Pinv == NULL: the Schur formation of the reference's QDLDL slot (form_schur_qdl_kernel,
+ * include/qdldl/linsys_setup.cuh:12-336): S, gamma and G^-1 only -- no theta inverse, no
+ * phase 2 (that slot never builds a preconditioner).
  * ------------------------------------------------------------------------- */
 void F(oracle_schur)(int s, int c, int N, REAL *G, const REAL *C, const REAL *g,
                      const REAL *cv, REAL rho, REAL *S, REAL *Pinv, REAL *gamma)
@@ -121,12 +124,12 @@ void F(oracle_schur)(int s, int c, int N, REAL *G, const REAL *C, const REAL *g,
     int k, i;
     memcpy(G0, G, sizeof(REAL) * Gsize);
     memset(S, 0, sizeof(REAL) * 3 * ss * N);
-    memset(Pinv, 0, sizeof(REAL) * 3 * ss * N);
+    if (Pinv) memset(Pinv, 0, sizeof(REAL) * 3 * ss * N);
 
     /* ---- phase 1, block row 0: linsys_setup.cuh:152-278 ---- */
     memcpy(Qk, G0, sizeof(REAL) * ss);
     for (i = 0; i < s; i++) Qk[i + i * s] += rho;                 /* :180 */
-    for (i = 0; i < ss; i++) F(bd)(Pinv, s, 0, 1)[i] = -Qk[i];    /* :202-210 (before inversion) */
+    if (Pinv) for (i = 0; i < ss; i++) F(bd)(Pinv, s, 0, 1)[i] = -Qk[i];    /* :202-210 (before inversion) */
     F(gj_invert)(s, Qk, Qk_i, 1);                                 /* :215-217 (2-matrix form) */
     F(matvec)(s, s, Qk_i, g, gam);                                /* :260-264 */
     for (i = 0; i < ss; i++) F(bd)(S, s, 0, 1)[i] = -Qk_i[i];     /* :249-255 */
@@ -164,8 +167,10 @@ void F(oracle_schur)(int s, int c, int N, REAL *G, const REAL *C, const REAL *g,
         for (i = 0; i < ss; i++) theta[i] += tmp[i];              /* :485-487 */
         for (i = 0; i < ss; i++) F(bd)(S, s, k, 0)[i] = -phi[i];  /* :491-497 */
         for (i = 0; i < ss; i++) F(bd)(S, s, k, 1)[i] = -theta[i];/* :501-507 */
-        F(gj_invert)(s, theta, thetaInv, 0);                      /* :511-513 (single form) */
-        for (i = 0; i < ss; i++) F(bd)(Pinv, s, k, 1)[i] = -thetaInv[i]; /* :518-524 */
+        if (Pinv) {
+            F(gj_invert)(s, theta, thetaInv, 0);                  /* :511-513 (single form) */
+            for (i = 0; i < ss; i++) F(bd)(Pinv, s, k, 1)[i] = -thetaInv[i]; /* :518-524 */
+        }
         for (i = 0; i < s; i++) gamma[(size_t)k * s + i] = -gam[i];      /* :529-532 */
         {   /* :537-557  S[k-1][2] = -(phi)^T */
             int r, q;
@@ -176,7 +181,7 @@ void F(oracle_schur)(int s, int c, int N, REAL *G, const REAL *C, const REAL *g,
     }
 
     /* ---- phase 2: linsys_setup.cuh:9-137 ---- */
-    for (k = 0; k < N; k++) {
+    for (k = 0; Pinv && k < N; k++) {
         const REAL *thInv_k = F(bd)(Pinv, s, k, 1);
         if (k != 0) {                                             /* :97-115 */
             F(gemm)(s, s, s, thInv_k, F(bd)(S, s, k, 0), tmp, 0);
@@ -337,6 +342,58 @@ void F(oracle_pcg_mode)(int s, int N, const REAL *S, const REAL *Pinv, const REA
     free(r);
 #undef BDMV
 #undef DOT
+}
+
+/* ---------------------------------------------------------------------------
+ * Single-reduction PCG (Chronopoulos & Gear 1989): the same Krylov iterates in exact
+ * arithmetic, with the two inner products of an iteration (r.u and u.Su, u = Pinv r)
+ * available together, so that a parallel implementation pays ONE global reduction per
+ * iteration instead of two:   p.Sp = u.Su - beta^2 (p.Sp)_old.
+ * Exit test, iteration count and max_iter flag as oracle_pcg.  This is the checker of the
+ * product's MPCGPU_B200_PCG_VARIANT=1 kernels; oracle_pcg stays the statement of the
+ * reference's iteration.
+ * ------------------------------------------------------------------------- */
+void F(oracle_pcg_cg1)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,
+                       REAL *lambda, unsigned max_iter, REAL exit_tol,
+                       unsigned *iters_out, unsigned char *max_iter_exit_out)
+{
+    const size_t n = (size_t)s * N;
+    REAL *r = (REAL *)calloc(n * 5, sizeof(REAL));
+    REAL *p = r + n, *q = p + n, *u = q + n, *w = u + n;     /* q = S p by recurrence */
+    REAL gam, del, gam_old = (REAL)1, c_old = (REAL)0;       /* c = (p.Sp) / (r.u)^2 of the previous iteration */
+    unsigned iter = 0;
+    unsigned char max_iter_exit = 1;
+    size_t i;
+
+    F(oracle_bdmv)(s, N, S, lambda, w);
+    for (i = 0; i < n; i++) r[i] = gamma[i] - w[i];
+    F(oracle_bdmv)(s, N, Pinv, r, u);
+    F(oracle_bdmv)(s, N, S, u, w);
+    gam = F(dot)(n, r, u);
+    del = F(dot)(n, u, w);
+    for (iter = 0; iter < max_iter; iter++) {
+        const REAL v = del - (gam * gam) * c_old;            /* p.Sp = u.Su - beta^2 (p.Sp)_old */
+        const REAL beta = iter ? gam / gam_old : (REAL)0;
+        REAL alpha;
+        if (v == (REAL)0) { max_iter_exit = 0; break; }
+        alpha = gam / v;
+        for (i = 0; i < n; i++) {
+            p[i] = u[i] + beta * p[i];
+            q[i] = w[i] + beta * q[i];
+            lambda[i] += alpha * p[i];
+            r[i] -= alpha * q[i];
+        }
+        c_old = (v / gam) / gam;
+        gam_old = gam;
+        F(oracle_bdmv)(s, N, Pinv, r, u);
+        F(oracle_bdmv)(s, N, S, u, w);
+        gam = F(dot)(n, r, u);
+        del = F(dot)(n, u, w);
+        if (FABS(gam) < exit_tol) { iter++; max_iter_exit = 0; break; }
+    }
+    *iters_out = iter;
+    *max_iter_exit_out = max_iter_exit;
+    free(r);
 }
 
 /* ---------------------------------------------------------------------------

@@ -12,6 +12,9 @@
 //   ref_harness schur <N> <rho> <in.bin> <out.bin>
 //        the reference's OWN form_schur_system<float> (include/pcg/linsys_setup.cuh:620-657)
 //        on in.bin = [G | C | g | c] -> out.bin = [S | Pinv | gamma | Ginv]
+//   ref_harness schur_shim <N> <rho> <in.bin> <out.bin>
+//        the same through the header shim's stage 1 (mpcb200_shim::form_schur_system_n, the function the
+//        unchanged include/pcg/sqp.cuh:243 binds to under the L1 shim): same file formats
 //   ref_harness pcg   <N> <tol> <max_iter> <in.bin> <out.bin>
 //        the header shim's pcg<float,14,N>, launched EXACTLY like include/pcg/sqp.cuh:275
 //        (cooperative, grid = N, block = PCG_NUM_THREADS, pcgSharedMemSize) on
@@ -31,6 +34,7 @@
 #include <cooperative_groups.h>
 
 #include "settings.cuh"
+#define MPCGPU_B200_SHIM_KEEP_REFERENCE_SCHUR 1   // form_schur_system<float> below must stay the REFERENCE's kernel
 #include "gpu_pcg.cuh"
 #include "common/kkt.cuh"            // (also defines the cgrps alias linsys_setup.cuh relies on)
 #include "pcg/linsys_setup.cuh"
@@ -110,7 +114,12 @@ static int do_kkt(uint32_t N, uint32_t row0, float perturb, const char* out) {
     return 0;
 }
 
-static int do_schur(uint32_t N, float rho, const char* in, const char* out) {
+template <uint32_t N>
+static void shim_schur_n(float* d_G, float* d_C, float* d_g, float* d_c, float* d_S, float* d_P, float* d_gamma, float rho) {
+    mpcb200_shim::form_schur_system_n<float, N>(d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho);
+}
+
+static int do_schur(uint32_t N, float rho, const char* in, const char* out, bool shim = false) {
     Sizes z(N);
     auto h = read_bin(in);
     if (h.size() != z.G + z.C + z.g + z.c) { fprintf(stderr, "bad input size\n"); return 3; }
@@ -121,7 +130,15 @@ static int do_schur(uint32_t N, float rho, const char* in, const char* out) {
     float *d_S, *d_P, *d_gamma;
     gpuErrchk(cudaMalloc(&d_S, z.S * 4)); gpuErrchk(cudaMalloc(&d_P, z.S * 4)); gpuErrchk(cudaMalloc(&d_gamma, z.v * 4));
     gpuErrchk(cudaMemset(d_S, 0, z.S * 4)); gpuErrchk(cudaMemset(d_P, 0, z.S * 4));   // corner blocks are never written
-    form_schur_system<float>(14, 7, N, d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho);   // the reference's own kernel
+    if (!shim) form_schur_system<float>(14, 7, N, d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho);   // the reference's own kernel
+    else switch (N) {
+        case 8: shim_schur_n<8>(d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho); break;
+        case 32: shim_schur_n<32>(d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho); break;
+        case 64: shim_schur_n<64>(d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho); break;
+        case 128: shim_schur_n<128>(d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho); break;
+        case 512: shim_schur_n<512>(d_G, d_C, d_g, d_c, d_S, d_P, d_gamma, rho); break;
+        default: fprintf(stderr, "schur_shim: N must be 8, 32, 64, 128 or 512\n"); return 3;
+    }
     gpuErrchk(cudaPeekAtLastError());
     gpuErrchk(cudaDeviceSynchronize());
     std::vector<float> o;
@@ -169,6 +186,7 @@ static int do_pcg_n(float tol, uint32_t max_iter, const char* in, const char* ou
 int main(int argc, char** argv) {
     if (argc >= 6 && !strcmp(argv[1], "kkt")) return do_kkt(atoi(argv[2]), atoi(argv[3]), atof(argv[4]), argv[5]);
     if (argc >= 6 && !strcmp(argv[1], "schur")) return do_schur(atoi(argv[2]), atof(argv[3]), argv[4], argv[5]);
+    if (argc >= 6 && !strcmp(argv[1], "schur_shim")) return do_schur(atoi(argv[2]), atof(argv[3]), argv[4], argv[5], true);
     if (argc >= 7 && !strcmp(argv[1], "pcg")) {
         const int N = atoi(argv[2]); const float tol = atof(argv[3]); const uint32_t mi = atoi(argv[4]);
         switch (N) {

@@ -188,7 +188,13 @@ def test_golden_fixture_through_gpu(golden_dir):
     assert rel(Gi[0].cpu().numpy(), z["Ginv64"]) < 1e-4
     lam, it, ex = gpu_pcg(N, Sg, Pg, gam, z["lam0"][None], float(z["pcg_tol"]))
     assert abs(int(it[0]) - int(z["pcg_iters"])) <= 1
-    assert rel(lam[0], z["pcg_lambda_f32"]) < 2e-2
+    # lambda against the committed oracle lambda: 1e-4, widened to 3 x the measured fp32 floor of this input (the
+    # GPU's S differs from the fixture's in the last bits; kappa(S) amplifies that -- oracle/parity.py measures it)
+    from oracle import parity
+    sysd = parity.systems(N, z["G"], z["C"], z["g"], z["cvec"], float(z["rho"]))
+    r = parity.record(N, sysd, z["lam0"], float(z["pcg_tol"]), lam[0], int(it[0]), bool(ex[0]))
+    assert not parity.check(r), (parity.check(r), r["fp32_floor"])
+    assert rel(lam[0], z["pcg_lambda_f32"]) < max(1e-4, 3.0 * r["fp32_floor"]), r["fp32_floor"]
 
 
 def test_batched_full_size_properties():
@@ -221,7 +227,11 @@ def test_batched_full_size_properties():
     y[:, 1:] += torch.einsum("bkrc,bkc->bkr", blk[:, 1:, 0], l3[:, :-1])
     y[:, :-1] += torch.einsum("bkrc,bkc->bkr", blk[:, :-1, 2], l3[:, 1:])
     res = (y - gam.view(B, N, S)).flatten(1).norm(dim=1) / gam.norm(dim=1)
-    assert float(res.max()) < 1.0 and float(res.median()) < 0.5
+    # every instance: the relative residual the oracle reaches on this workload at tol 1e-4 is 0.073 ... 0.088
+    # (gpurun_out/parity_r2.jsonl, 32 sampled instances; the exit test is ABSOLUTE on r.Pinv r and ||gamma|| is
+    # small here) -- all 4096 must land in that band; the per-instance criteria (iterations, residual and lambda
+    # against the fp64 run, measured floors) are asserted on sampled instances in test_gpu_operating_point.py
+    assert float(res.max()) < 0.2 and float(res.min()) > 0.03, (float(res.min()), float(res.max()))
     # single-instance equality + permutation
     perm = torch.randperm(B, device=DEV)
     G2 = G0[perm].contiguous()
