@@ -310,26 +310,19 @@ def f64_leg(torch, mg, N, B, tol):
             "single_fused_us": us, "single_fused_iters": int(it[0].item())}
 
 
-def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, reps=30):
-    """BASELINE.json configs[3]: one N-knot horizon split by knot range over the `world` GPUs
-    (NVLink peer mailboxes, no collective call inside the solve).  Stream-timed, max over ranks."""
+def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, grp, reps=30, check=True):
+    """BASELINE.json configs[3]: one N-knot horizon split by knot range over the `world` GPUs (NVLink peer
+    mailboxes, no collective call inside the solve).  Stream-timed, max over ranks.  Rank 0 checks the gathered
+    lambda against the oracle PCG on the full horizon (outside the timed region)."""
     from mpcgpu_b200 import synth
     d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + N)
     lo, hi = mg.knot_range(N, rank, world)
-    lo_e, hi_e, off = mg.schur_slice(N, rank, world)
-    ne, n = hi_e - lo_e, hi - lo
-    ze = mg.sizes(S, C, ne)
-    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)[None]
-    G = t(d["G"][0][lo_e * 245: lo_e * 245 + ze["G"]]); Cm = t(d["C"][0][lo_e * 294: lo_e * 294 + ze["C"]])
-    g = t(d["g"][0][lo_e * 21: lo_e * 21 + ze["g"]]); cv = t(d["c"][0][lo_e * 14: lo_e * 14 + ze["c"]])
-    Se = torch.empty((1, ze["S"]), device=dev); Pe = torch.empty_like(Se); ge = torch.empty((1, ze["gamma"]), device=dev)
-    mg.form_schur_system(S, C, ne, G, Cm, g, cv, Se, Pe, ge, d["rho"])
-    Sl = Se[0, off * 588:(off + n) * 588].contiguous(); Pl = Pe[0, off * 588:(off + n) * 588].contiguous()
-    gl = ge[0, off * 14:(off + n) * 14].contiguous()
+    n = hi - lo
+    t1 = lambda a: torch.from_numpy(np.ascontiguousarray(a))
+    Sl, Pl, gl = mg.schur_rows_local(S, C, N, rank, world, t1(d["G"][0]), t1(d["C"][0]), t1(d["g"][0]), t1(d["c"][0]), d["rho"])
     lam = torch.zeros(n * 14, device=dev)
     it = torch.zeros(1, dtype=torch.int32, device=dev); ex = torch.zeros(1, dtype=torch.uint8, device=dev)
     cfg = mg.PcgConfig(pcg_exit_tol=tol)
-    grp = mg.KnotSplitGroup()
     for _ in range(3):
         lam.zero_(); grp.pcg(S, n, Sl, Pl, gl, lam, it, ex, cfg)
     torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
@@ -341,10 +334,95 @@ def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, reps=30):
     tt = torch.tensor([e0.elapsed_time(e1) / reps * 1e3], device=dev, dtype=torch.float64)
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     iters = int(it.item())
-    grp.close()
-    return {"knot_points": N, "knots_per_gpu": n, "solve_us": float(tt[0]), "iters": iters,
-            "us_per_iter": float(tt[0]) / max(iters, 1), "max_iter_exit": int(ex.item()),
-            "exchange": "tagged 8-byte NVLink peer stores into per-GPU mailboxes, polled locally; no NCCL in the solve"}
+    out = {"knot_points": N, "knots_per_gpu": n, "solve_us": float(tt[0]), "iters": iters,
+           "us_per_iter": float(tt[0]) / max(iters, 1), "max_iter_exit": int(ex.item()),
+           "exchange": "tagged 8-byte NVLink peer stores into per-GPU mailboxes, polled locally; no NCCL in the solve"}
+    if check:
+        parts = [torch.zeros_like(lam) for _ in range(world)]
+        dist.all_gather(parts, lam)
+        if rank == 0:
+            import oracle
+            lam_g = torch.cat(parts).cpu().numpy()
+            S32, P32, g32, _ = oracle.schur(S, C, N, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], np.float32)
+            l0 = np.zeros(S * N, np.float32)
+            _, it_o, _ = oracle.pcg(S, N, S32, P32, g32, l0, 10000, tol)
+            lam_s, _, _ = oracle.pcg(S, N, S32, P32, g32, l0, iters, 0.0)
+            out["parity"] = {"oracle_iters": it_o, "iters_within_1": bool(abs(iters - it_o) <= 1),
+                             "lambda_rel_vs_oracle_same_iters": float(np.linalg.norm(lam_g - lam_s) / np.linalg.norm(lam_s)),
+                             "fp32_floor": float(oracle.pcg_noise_floor(S, N, S32, P32, g32, l0, iters))}
+    return out
+
+
+def nccl_exchange_floor(torch, dist, rank, world, dev, iters=200):
+    """SURVEY 8(e) "baseline to beat": what the knot split's two exchanges per PCG iteration cost when they go through
+    NCCL -- all_reduce of the partial sums + send/recv of the 14-float boundary rows to both neighbours, twice per
+    iteration, NO compute.  CUDA events, max over ranks; microseconds per PCG iteration."""
+    red = torch.zeros(2, device=dev)
+    out_l, in_l, out_r, in_r = (torch.zeros(14, device=dev) for _ in range(4))
+
+    def one():
+        for _ in range(2):
+            dist.all_reduce(red)
+            ops = []
+            if rank > 0:
+                ops += [dist.P2POp(dist.isend, out_l, rank - 1), dist.P2POp(dist.irecv, in_l, rank - 1)]
+            if rank + 1 < world:
+                ops += [dist.P2POp(dist.isend, out_r, rank + 1), dist.P2POp(dist.irecv, in_r, rank + 1)]
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+    for _ in range(20):
+        one()
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        one()
+    e1.record(); torch.cuda.synchronize()
+    tt = torch.tensor([e0.elapsed_time(e1) / iters * 1e3], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    return float(tt[0])
+
+
+def knotsplit_leg(torch, mg, dist, rank, world, dev, tol):
+    """Everything measured about the knot-range split at `world` GPUs; failures are reported, never fatal."""
+    out = {}
+    grp = None
+    try:
+        grp = mg.KnotSplitGroup()
+        out["mailbox_one_way_us"] = grp.pingpong_us()
+        out["exchange_floor_us_per_iter"] = 2.0 * out["mailbox_one_way_us"]
+        if 512 % world == 0 and 512 // world in (64, 128, 256):
+            out["n512"] = knotsplit_bench(torch, mg, dist, rank, world, dev, 512, tol, grp)
+        out["n512_per_gpu"] = knotsplit_bench(torch, mg, dist, rank, world, dev, 512 * world, tol, grp, reps=10)
+    except Exception as e:      # noqa: BLE001
+        out["error"] = repr(e)[:300]
+    finally:
+        if grp is not None:
+            try:
+                grp.close()
+            except Exception:   # noqa: BLE001
+                pass
+    try:
+        out["nccl_exchange_us_per_iter"] = nccl_exchange_floor(torch, dist, rank, world, dev)
+    except Exception as e:      # noqa: BLE001
+        out["nccl_error"] = repr(e)[:300]
+    return out
+
+
+def e2e_producer_leg(N, B, tol, steps, local):
+    """VERDICT r1 "Next" #5: the same metric end to end with the KKT PRODUCER on the device -- the host ships each
+    instance's iterate, start state and goal window (~7 KB) instead of its KKT blocks (149 KB) and reads back dz.
+    Runs mpcgpu_b200/_plugins/e2e_producer (tools/e2e_producer.cu: reference GRiD dynamics in the batched producer ->
+    fused Schur + PCG + dz), built where the reference's headers exist; one process per rank, all ranks at once."""
+    exe = os.path.join(ROOT, "mpcgpu_b200", "_plugins", "e2e_producer")
+    if not os.path.exists(exe):
+        return {"unavailable": "mpcgpu_b200/_plugins/e2e_producer not built (needs the reference's dynamics headers)"}
+    env = dict(os.environ, LD_LIBRARY_PATH="/usr/local/cuda/lib64:" + os.environ.get("LD_LIBRARY_PATH", ""))
+    r = subprocess.run([exe, str(N), str(B), str(tol), str(steps), "3", str(local)], cwd=os.path.dirname(exe), env=env,
+                       capture_output=True, text=True, timeout=600)
+    if r.returncode != 0:
+        return {"error": (r.stdout[-200:] + r.stderr[-200:])}
+    return json.loads(r.stdout.strip().splitlines()[-1])
 
 
 def parity_block(N, d, lam, it, ex, tol, samples):
@@ -509,6 +587,14 @@ def main():
         e2e_s = float(tt[0])
     clocks = sampler.stop() if sampler else None
     assert torch.equal(hl.to(dev), lam), "host path and device path disagree"
+    barrier()
+    ep = e2e_producer_leg(N, B, a.tol, a.steps, local)          # every rank at once (shared host), own process per rank
+    if dist is not None and "solves_per_s" in ep:
+        tt = torch.tensor([ep["solves_per_s"]], device=dev, dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+        ep["solves_per_s_all_gpus"] = float(tt[0]) * world        # slowest rank x ranks
+    elif "solves_per_s" in ep:
+        ep["solves_per_s_all_gpus"] = ep["solves_per_s"]
     h2d = 4 * B * (hG[0].numel() + hC[0].numel() + hg[0].numel() + hc[0].numel() + S * N)
     d2h = B * (4 * S * N + 4 + 1)
     hs.close()
@@ -537,8 +623,8 @@ def main():
     del probe_h, probe_d
 
     ks = None
-    if world > 1 and not a.no_extras and 512 % world == 0 and 512 // world in (64, 128, 256):
-        ks = knotsplit_bench(torch, mg, dist, rank, world, dev, 512, a.tol)
+    if world > 1 and not a.no_extras:
+        ks = knotsplit_leg(torch, mg, dist, rank, world, dev, a.tol)
     if rank == 0:
         peak, how = load_peaks()
         ms_per_step = total_ms / a.steps
@@ -588,6 +674,7 @@ def main():
                 line["two_stage"] = two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, a.tol, peak)
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
                 line["f64"] = f64_leg(torch, mg, N, min(B, 1024), a.tol)
+        line["e2e_producer"] = ep
         if per_rank is not None:
             line["per_rank"] = per_rank
         if ks is not None:

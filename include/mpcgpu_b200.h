@@ -196,9 +196,21 @@ int mpcgpu_b200_solver_solve_host_io_f32(mpcgpu_b200_solver* solver, uint32_t ba
  * boundary inside the solve.  d_mailboxes: HOST array of `world` device pointers (this rank's
  * own mailbox and the peers' mailboxes mapped with mpcgpu_b200_ipc_open), each
  * mpcgpu_b200_knotsplit_mailbox_bytes() long and zeroed once.  `epoch` must be identical on
- * all ranks and grow by more than 2*max_iter+8 from one solve to the next.
+ * all ranks and grow from one solve to the next by an ODD amount larger than 2*max_iter+8
+ * (mpcgpu_b200_knotsplit_epoch_stride(max_iter)): the tags of a solve are epoch + exchange counter, and
+ * the parity of `epoch` selects which half of every mailbox the solve uses, so that a rank that has
+ * already entered the next solve never overwrites a slot a slower rank has not read yet.
+ * A poll that waits longer than MPCGPU_B200_KNOTSPLIT_TIMEOUT_MS (default 30000) for a peer records
+ * {1, rank, expected tag, seen tag} for mpcgpu_b200_knotsplit_last_timeout() and traps (the launch
+ * fails with a CUDA error on this rank instead of hanging the GPU).
  * ranks_here > 1 emulates several ranks in one cooperative launch on ONE GPU (tests). */
 size_t mpcgpu_b200_knotsplit_mailbox_bytes(void);
+uint32_t mpcgpu_b200_knotsplit_epoch_stride(uint32_t max_iter);
+int mpcgpu_b200_knotsplit_last_timeout(uint32_t out[4]);   /* returns 1 if a poll of this process timed out */
+/* Latency floor of one exchange: `reps` round trips of one tagged 8-byte peer store + local poll between two
+ * ranks (me = 0 / 1) through the last slot of their mailboxes; *d_out_ns = device wall time of the reps. */
+int mpcgpu_b200_knotsplit_pingpong(uint32_t me, void* d_my_mailbox, void* d_peer_mailbox, uint32_t reps,
+                                   uint32_t tag0, unsigned long long* d_out_ns, void* stream);
 /* a zeroed mailbox in its OWN cudaMalloc allocation (an IPC handle names a whole allocation) */
 int mpcgpu_b200_knotsplit_mailbox_create(void** d_mailbox);
 int mpcgpu_b200_knotsplit_mailbox_destroy(void* d_mailbox);

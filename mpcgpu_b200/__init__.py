@@ -9,7 +9,7 @@ include/pcg/sqp.cuh), synth.py (seeded synthetic KKT blocks).
 from . import synth  # noqa: F401
 from .api import (HostSolver, KnotSplitGroup, MpcGpuError, PcgConfig, epoch_stride,  # noqa: F401
                   compute_dz, form_schur_system, kkt_solve, kkt_solve_dz, knot_range, knotsplit_pcg, launch_count, lib,
-                  mailbox_bytes, pcg, schur_slice, sizes)
+                  mailbox_bytes, pcg, schur_rows_local, schur_slice, sizes, knotsplit_last_timeout)
 
 __all__ = ["HostSolver", "MpcGpuError", "PcgConfig", "form_schur_system", "kkt_solve", "kkt_solve_dz", "compute_dz", "pcg",
            "sizes", "synth", "lib", "launch_count"]

@@ -272,6 +272,36 @@ def schur_slice(knot_points, rank, world):
     return lo_e, hi_e, lo - lo_e
 
 
+def schur_rows_local(state_size, control_size, knot_points, rank, world, G, C, g, c, rho):
+    """S / Pinv / gamma block rows of the knots `rank` owns, formed on THIS device from its slice of the full-horizon
+    inputs (host or device 1-D float32 tensors G, C, g, c of the whole horizon) with no communication.  Ranges longer
+    than one form_schur_system call can take (512 knots incl. the 2 + 1 halo knots of :func:`schur_slice`) are
+    formed in sub-ranges; every row is bit-identical to the full-horizon computation.
+    Returns (S_local, Pinv_local, gamma_local) as contiguous device tensors."""
+    s, cc, N = state_size, control_size, knot_points
+    lo, hi = knot_range(N, rank, world)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    nG, nC, ng = s * s + cc * cc, s * s + s * cc, s + cc
+    S_l = torch.empty(3 * s * s * (hi - lo), device=dev)
+    P_l = torch.empty_like(S_l)
+    g_l = torch.empty(s * (hi - lo), device=dev)
+    step = 500
+    for a in range(lo, hi, step):
+        b = min(a + step, hi)
+        lo_e, hi_e = max(a - 2, 0), min(b + 1, N)
+        ne, off = hi_e - lo_e, a - lo_e
+        z = sizes(s, cc, ne)
+        cut = lambda t, per, n: t[lo_e * per: lo_e * per + n].to(dev, non_blocking=True).contiguous()[None].clone()
+        Ge, Ce, ge, ce = cut(G, nG, z["G"]), cut(C, nC, z["C"]), cut(g, ng, z["g"]), cut(c, s, z["c"])
+        Se = torch.empty((1, z["S"]), device=dev); Pe = torch.empty_like(Se); gme = torch.empty((1, z["gamma"]), device=dev)
+        form_schur_system(s, cc, ne, Ge, Ce, ge, ce, Se, Pe, gme, rho)
+        w = 3 * s * s
+        S_l[(a - lo) * w:(b - lo) * w] = Se[0, off * w:(off + b - a) * w]
+        P_l[(a - lo) * w:(b - lo) * w] = Pe[0, off * w:(off + b - a) * w]
+        g_l[(a - lo) * s:(b - lo) * s] = gme[0, off * s:(off + b - a) * s]
+    return S_l, P_l, g_l
+
+
 def mailbox_bytes():
     lib().mpcgpu_b200_knotsplit_mailbox_bytes.restype = ctypes.c_size_t
     return int(lib().mpcgpu_b200_knotsplit_mailbox_bytes())
@@ -297,7 +327,18 @@ def knotsplit_pcg(state_size, knots_local, ranks_here, rank_first, world, epoch,
 
 
 def epoch_stride(config: PcgConfig):
-    return 2 * int(config.pcg_max_iter) + 16
+    """Epoch increment between consecutive solves of a group: odd (alternates the mailbox half) and larger than
+    the number of tags a solve can use."""
+    lib().mpcgpu_b200_knotsplit_epoch_stride.restype = ctypes.c_uint32
+    return int(lib().mpcgpu_b200_knotsplit_epoch_stride(ctypes.c_uint32(int(config.pcg_max_iter))))
+
+
+def knotsplit_last_timeout():
+    """{rank, expected_tag, seen_tag} of a peer poll of this process that timed out, else None."""
+    out = (ctypes.c_uint32 * 4)()
+    if lib().mpcgpu_b200_knotsplit_last_timeout(out):
+        return {"rank": int(out[1]), "expected_tag": int(out[2]), "seen_tag": int(out[3])}
+    return None
 
 
 class KnotSplitGroup:
@@ -331,6 +372,23 @@ class KnotSplitGroup:
         knotsplit_pcg(state_size, knots_local, 1, self.rank, self.world, self.epoch, self.ptrs, d_S, d_Pinv,
                       d_gamma, d_lambda, d_iters, d_exit, config)
         self.epoch += epoch_stride(config)
+
+    def pingpong_us(self, reps=2000):
+        """One-way latency (us) of ONE tagged 8-byte peer store + local poll between ranks 0 and 1 over NVLink:
+        the floor of a knot-split exchange.  Collective: every rank of the group calls it; ranks >= 2 idle."""
+        out = torch.zeros(1, dtype=torch.int64, device="cuda")
+        self.epoch += 2 * reps + 17
+        if self.rank < 2 and self.world >= 2:
+            peer = self.ptrs[1 - self.rank]
+            _check(lib().mpcgpu_b200_knotsplit_pingpong(
+                ctypes.c_uint32(self.rank), ctypes.c_void_p(self.ptrs[self.rank]), ctypes.c_void_p(peer),
+                ctypes.c_uint32(reps), ctypes.c_uint32(self.epoch), ctypes.c_void_p(out.data_ptr()), _stream()), "knotsplit_pingpong")
+        torch.cuda.synchronize()
+        self.epoch += 2 * reps + 18          # keeps the odd stride of the solves that follow
+        self.dist.barrier(group=self.group)
+        t = out.to(torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX, group=self.group)
+        return float(t[0]) / (2.0 * reps) * 1e-3
 
     def close(self):
         torch.cuda.synchronize()

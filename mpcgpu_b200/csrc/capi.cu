@@ -303,6 +303,63 @@ extern "C" {
 
 size_t mpcgpu_b200_knotsplit_mailbox_bytes(void) { return sizeof(uint2) * SPLIT_MAIL_U2; }
 
+uint32_t mpcgpu_b200_knotsplit_epoch_stride(uint32_t max_iter) { return 2u * max_iter + 17u; }   // odd, > 2*max_iter + 8
+
+// host-visible record of a poll that timed out: {flag, rank, expected tag, seen tag}; pinned, one per process
+static unsigned* split_diag() {
+    static unsigned* h = [] {
+        unsigned* p = nullptr;
+        if (cudaHostAlloc((void**)&p, 4 * sizeof(unsigned), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return (unsigned*)nullptr; }
+        memset(p, 0, 4 * sizeof(unsigned));
+        return p;
+    }();
+    return h;
+}
+
+int mpcgpu_b200_knotsplit_last_timeout(uint32_t out[4]) {
+    unsigned* h = split_diag();
+    for (int i = 0; i < 4; i++) out[i] = h ? h[i] : 0u;
+    return h && h[0] ? 1 : 0;
+}
+
+}  // extern "C"
+
+// ---- NVLink mailbox floor: one tagged 8-byte peer store + local poll per hop, nothing else ----------------
+namespace {
+__global__ void pingpong_kernel(uint2* mine, uint2* peer, unsigned me, unsigned reps, unsigned tag0,
+                                unsigned long long timeout_ns, unsigned* diag, unsigned long long* out_ns) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    SplitCtx X{me, 2u, tag0, nullptr, 0u, timeout_ns, diag};
+    unsigned long long t0 = 0;
+    for (unsigned i = 0; i <= reps; i++) {           // hop 0 is the rendezvous (the peer kernel may start later): not timed
+        const unsigned tag = tag0 + i + 1u;
+        if (me == 0) { sys_store_tagged(peer, (float)i, tag); (void)sys_poll_tagged(X, mine, tag); }
+        else         { (void)sys_poll_tagged(X, mine, tag); sys_store_tagged(peer, (float)i, tag); }
+        if (i == 0) t0 = globaltimer_ns();
+    }
+    *out_ns = globaltimer_ns() - t0;
+}
+}  // namespace
+
+extern "C" {
+
+// `reps` round trips between two ranks (me = 0 starts) through the LAST slot of their mailboxes; *d_out_ns = the
+// kernel's own wall time over the reps (one-way latency = ns / (2 reps)).  The latency floor of one knot-split
+// exchange: every PCG iteration of the split pays two such hops.
+int mpcgpu_b200_knotsplit_pingpong(uint32_t me, void* d_my_mailbox, void* d_peer_mailbox, uint32_t reps, uint32_t tag0,
+                                   unsigned long long* d_out_ns, void* stream) {
+    if (me > 1 || !d_my_mailbox || !d_peer_mailbox || !d_out_ns || reps < 1) return bad("mpcgpu_b200_knotsplit_pingpong: bad argument");
+    unsigned* diag = nullptr;
+    if (unsigned* h = split_diag()) { if (cudaHostGetDevicePointer((void**)&diag, h, 0) != cudaSuccess) { cudaGetLastError(); diag = nullptr; } }
+    uint2* mine = (uint2*)d_my_mailbox + SPLIT_MAIL_U2 - 1;
+    uint2* peer = (uint2*)d_peer_mailbox + SPLIT_MAIL_U2 - 1;
+    pingpong_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(mine, peer, me, reps, tag0, 30000000000ull, diag, d_out_ns);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(e, "mpcgpu_b200_knotsplit_pingpong");
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    return 0;
+}
+
 int mpcgpu_b200_knotsplit_mailbox_create(void** d_mailbox) {
     // a dedicated cudaMalloc allocation: an IPC handle always names a whole allocation, so the
     // mailbox must not be carved out of a caching allocator's segment
@@ -349,6 +406,19 @@ int mpcgpu_b200_knotsplit_pcg_f32(uint32_t s, uint32_t knots_local, uint32_t ran
     SplitArgs a;
     memset(&a, 0, sizeof(a));
     a.n_local = (int)knots_local; a.grank_first = rank_first; a.world = world; a.epoch = epoch;
+    // consecutive solves alternate between the two halves of every mailbox: their epochs differ by an odd stride
+    a.parity = epoch & 1u;
+    static const unsigned long long timeout_ms = [] {
+        const char* e = getenv("MPCGPU_B200_KNOTSPLIT_TIMEOUT_MS");
+        const long long v = e ? atoll(e) : 0;
+        return (unsigned long long)(v > 0 ? v : 30000);
+    }();
+    a.timeout_ns = timeout_ms * 1000000ull;
+    a.diag = nullptr;
+    if (unsigned* h = split_diag()) {
+        unsigned* d = nullptr;
+        if (cudaHostGetDevicePointer((void**)&d, h, 0) == cudaSuccess) a.diag = d; else cudaGetLastError();
+    }
     for (uint32_t r = 0; r < world; r++) {
         if (!d_mailboxes[r]) return bad("mpcgpu_b200_knotsplit_pcg_f32: null mailbox");
         a.mail[r] = (uint2*)d_mailboxes[r];

@@ -194,6 +194,9 @@ __global__ void __launch_bounds__(256) dz_kernel(BatchArgsT<T> a) {
 struct SplitArgs {
     int n_local;                 // knots per rank (== KPC * CL)
     unsigned grank_first, world, epoch;
+    unsigned parity;             // half of every mailbox used by this solve (alternates between consecutive solves)
+    unsigned long long timeout_ns;
+    unsigned* diag;              // host-visible {flag, rank, expected tag, seen tag} of a timed-out poll (may be null)
     uint2* mail[SPLIT_MAXW];     // mailbox of every rank (local or peer-mapped)
     const float* S; const float* Pinv; const float* gamma; float* lambda;   // first local rank's slices
     unsigned max_iter; float exit_tol;
@@ -205,7 +208,7 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_split_kernel(SplitAr
     extern __shared__ float4 smem4[];
     float* smem = reinterpret_cast<float*>(smem4);
     const int c = blockIdx.x / CF::CL;                  // local rank index within this launch
-    SplitCtx X{a.grank_first + (unsigned)c, a.world, a.epoch, a.mail};
+    SplitCtx X{a.grank_first + (unsigned)c, a.world, a.epoch, a.mail, a.parity, a.timeout_ns, a.diag};
     const size_t ks = (size_t)c * a.n_local;
     RowsOf<CF> R;
     load_rows<CF>(smem, R, a.S + ks * 3 * 196, a.Pinv + ks * 3 * 196, a.gamma + ks * 14, a.n_local,

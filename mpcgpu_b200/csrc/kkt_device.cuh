@@ -794,29 +794,56 @@ __device__ __forceinline__ typename CF::T cluster_sum(typename CF::T* red, uint6
 // destination GPU's memory (NVLink peer stores) and are consumed by polling the LOCAL mailbox:
 // no host round trip, no NCCL call, no kernel boundary per iteration.  Tags are
 // epoch + exchange counter, so a mailbox never needs clearing between solves.
-// Mailbox layout (uint2 units): red[2 bufs][16 ranks] | hal[5 phases][2 sides][16 rows].
+// Mailbox layout (8-byte units): [2 solve parities] x ( red[2 bufs][16 ranks] | hal[5 phases][2 sides][16 rows] ).
+// Consecutive solves use alternating halves: a rank that is already in solve j+1 (it only needs its two
+// neighbours to get there) posts into the other half, so it can never overwrite a slot of solve j that a lagging
+// warp of a third rank has not read yet; half j is reused by solve j+2, which no rank can reach before every rank
+// has left solve j.  {value, tag} is ONE 64-bit store / load (single-copy atomic), never two words.
 // ---------------------------------------------------------------------------------------
 constexpr int SPLIT_MAXW = 16;
 constexpr int SPLIT_HAL0 = 2 * SPLIT_MAXW;
-constexpr int SPLIT_MAIL_U2 = SPLIT_HAL0 + 5 * 2 * 16;      // 192 x 8 B
+constexpr int SPLIT_HALF_U2 = SPLIT_HAL0 + 5 * 2 * 16;      // one parity: 192 x 8 B
+constexpr int SPLIT_MAIL_U2 = 2 * SPLIT_HALF_U2;            // 3 KB per rank
 struct SplitCtx {
     unsigned grank, world;     // this cluster's rank among the knot-range owners
     unsigned epoch;            // tag base of this solve (identical on all ranks, above all earlier tags)
     uint2* const* mail;        // [world] mailbox of every rank (local or peer-mapped device pointers)
+    unsigned parity;           // which half of every mailbox this solve uses
+    unsigned long long timeout_ns;   // how long a poll may wait for a peer (%globaltimer)
+    unsigned* diag;            // optional host-visible record of a timed-out poll: {1, rank, expected tag, seen tag}
 };
 __device__ __forceinline__ void sys_store_tagged(uint2* dst, float v, unsigned tag) {
-    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(dst), "r"(__float_as_uint(v)), "r"(tag) : "memory");
+    const unsigned long long w = (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
+    asm volatile("st.relaxed.sys.global.b64 [%0], %1;" ::"l"(dst), "l"(w) : "memory");
 }
-// bounded spin: a dead peer must not hang the GPU -- after ~seconds the kernel traps (a loud
-// CUDA error on this rank) instead of waiting forever
-__device__ __forceinline__ float sys_poll_tagged(const uint2* src, unsigned tag) {
-    for (unsigned spin = 0; spin < (1u << 23); spin++) {
-        unsigned a, b;
-        asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(a), "=r"(b) : "l"(src) : "memory");
-        if (b == tag) return __uint_as_float(a);
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+// A dead peer must not hang the GPU: a poll that waits longer than X.timeout_ns (wall clock, configurable through
+// MPCGPU_B200_KNOTSPLIT_TIMEOUT_MS, default 30 s -- a peer that is merely late, e.g. lazy module loading, is not
+// dead) records what it was waiting for in host-visible memory and traps: a loud CUDA error on this rank.
+static __device__ __noinline__ void sys_poll_timed_out(const SplitCtx& X, unsigned tag, unsigned seen) {
+    if (X.diag) {
+        X.diag[1] = X.grank; X.diag[2] = tag; X.diag[3] = seen;
+        __threadfence_system();
+        X.diag[0] = 1u;
+        __threadfence_system();
     }
     __trap();
-    return 0.f;
+}
+__device__ __forceinline__ float sys_poll_tagged(const SplitCtx& X, const uint2* src, unsigned tag) {
+    unsigned long long w, t0 = 0;
+    for (unsigned spin = 0;; spin++) {
+        asm volatile("ld.relaxed.sys.global.b64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+        if ((unsigned)(w >> 32) == tag) return __uint_as_float((unsigned)w);
+        if ((spin & 1023u) == 1023u) {                       // look at the clock every 1024 polls
+            const unsigned long long now = globaltimer_ns();
+            if (t0 == 0) t0 = now;
+            else if (now - t0 > X.timeout_ns) sys_poll_timed_out(X, tag, (unsigned)(w >> 32));
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -1027,12 +1054,12 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     };
     // my rows -> mailbox [phase][side] of rank `dst` (another GPU), tagged
     auto gpush = [&](int phase, int side, unsigned dst, unsigned tag, const T (&v)[RPT]) {
-        uint2* m = X->mail[dst] + SPLIT_HAL0 + (phase * 2 + side) * 16;
+        uint2* m = X->mail[dst] + X->parity * SPLIT_HALF_U2 + SPLIT_HAL0 + (phase * 2 + side) * 16;
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) sys_store_tagged(m + rm.row[j], v[j], tag);
     };
     auto gpull = [&](int phase, int side, int r, unsigned tag) {
-        return sys_poll_tagged(X->mail[X->grank] + SPLIT_HAL0 + (phase * 2 + side) * 16 + r, tag);
+        return sys_poll_tagged(*X, X->mail[X->grank] + X->parity * SPLIT_HALF_U2 + SPLIT_HAL0 + (phase * 2 + side) * 16 + r, tag);
     };
     // boundary rows of the neighbour RANKS -> my halo slots (pre-loop exchanges, phases 2..4)
     auto gpull_rows = [&](int phase, unsigned tag, T* left_slot, T* right_slot) {
@@ -1046,10 +1073,10 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     };
     // all-reduce of the per-rank totals (w is already identical in every thread of this cluster)
     auto gsum = [&](int buf, unsigned tag, T w) {
-        if (rank == 0 && tid < (int)X->world) sys_store_tagged(X->mail[tid] + buf * SPLIT_MAXW + X->grank, w, tag);
+        if (rank == 0 && tid < (int)X->world) sys_store_tagged(X->mail[tid] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + X->grank, w, tag);
         const int lane = tid & 31;
         T v = T(0);
-        if (lane < (int)X->world) v = sys_poll_tagged(X->mail[X->grank] + buf * SPLIT_MAXW + lane, tag);
+        if (lane < (int)X->world) v = sys_poll_tagged(*X, X->mail[X->grank] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + lane, tag);
         __syncwarp();
         return warp_sum(v);
     };
@@ -1236,7 +1263,11 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     if (last_g)  { if (has_r) push(hl_p, rank + 1, 1, pp); else if (gr) gpush(4, 0, X->grank + 1, tg0, pp); else put(hr_p, zero); }
     if (SPLIT) gpull_rows(4, tg0, hl_p, hr_p);
     T eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
-    if (SPLIT) { eta = gsum(1, ++gseq[1], eta); __syncthreads(); }
+    if (SPLIT) eta = gsum(1, ++gseq[1], eta);
+    // the p rows stored above are read by OTHER warps in the first S p: for CL > 1 the reduction ends on an
+    // mbarrier wait, which orders the st.async bytes only, so the ordinary stores need a CTA barrier of their own
+    // (CL == 1: cluster_sum already contains one); once per solve
+    if (CL > 1 || SPLIT) __syncthreads();
 
     for (; iter < max_iter; iter++) {
         // ---- ups = S p ; v = p.ups -----------------------------------------------------------

@@ -13,6 +13,8 @@
 #include <new>
 #include <string>
 
+#include "capi_internal.h"
+
 struct mpcgpu_b200_solver {
     int device;
     uint32_t s, c, N, max_batch;
@@ -27,7 +29,9 @@ struct mpcgpu_b200_solver {
 };
 
 namespace {
-int sfail(cudaError_t e) { return (int)e; }
+// every failure leaves its text in mpcgpu_b200_last_error(), like the other entry points of the ABI
+int sfail(cudaError_t e, const char* what = "mpcgpu_b200_solver") { return mpcb200::detail::fail(e, what); }
+int sbad(const char* what) { return mpcb200::detail::bad(what); }
 }  // namespace
 
 extern "C" {
@@ -35,11 +39,11 @@ extern "C" {
 int mpcgpu_b200_solver_create(mpcgpu_b200_solver** out, int device, uint32_t s, uint32_t c,
                               uint32_t N, uint32_t max_batch) {
     if (!out || s != 14 || c != 7 || N < 1 || N > 512 || max_batch < 1)
-        return (int)cudaErrorInvalidValue;
+        return sbad("mpcgpu_b200_solver_create: need out != NULL, s=14, c=7, 1<=N<=512, max_batch>=1");
     cudaError_t e = cudaSetDevice(device);
-    if (e != cudaSuccess) return sfail(e);
+    if (e != cudaSuccess) return sfail(e, "mpcgpu_b200_solver_create: cudaSetDevice");
     mpcgpu_b200_solver* S = new (std::nothrow) mpcgpu_b200_solver();
-    if (!S) return (int)cudaErrorMemoryAllocation;
+    if (!S) return sfail(cudaErrorMemoryAllocation, "mpcgpu_b200_solver_create");
     memset(S, 0, sizeof(*S));
     S->device = device; S->s = s; S->c = c; S->N = N; S->max_batch = max_batch;
     S->nG = (size_t)(s * s + c * c) * N - c * c;
@@ -70,7 +74,7 @@ int mpcgpu_b200_solver_create(mpcgpu_b200_solver** out, int device, uint32_t s, 
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&S->st_out, cudaStreamNonBlocking);
     if (e != cudaSuccess) {
         mpcgpu_b200_solver_destroy(S);
-        return sfail(e);
+        return sfail(e, "mpcgpu_b200_solver_create: device buffers / streams");
     }
     *out = S;
     return 0;
@@ -108,12 +112,12 @@ int mpcgpu_b200_solver_solve_host_io_f32(mpcgpu_b200_solver* S, uint32_t batch, 
                                          uint8_t* h_exit, float* h_Ginv) {
     if (!S || batch < 1 || batch > S->max_batch || !h_G || (S->N > 1 && !h_C) || !h_g || !h_c ||
         !h_lambda || !h_iters || !h_exit)
-        return (int)cudaErrorInvalidValue;
+        return sbad("mpcgpu_b200_solver_solve_host: null pointer or batch outside [1, max_batch]");
     cudaError_t e = cudaSetDevice(S->device);
-    if (e != cudaSuccess) return sfail(e);
+    if (e != cudaSuccess) return sfail(e, "mpcgpu_b200_solver_solve_host: cudaSetDevice");
     constexpr int NBUF = mpcgpu_b200_solver::NBUF;
     const uint32_t nchunks = (batch + S->chunk - 1) / S->chunk;
-#define CK(x) do { e = (x); if (e != cudaSuccess) return sfail(e); } while (0)
+#define CK(x) do { e = (x); if (e != cudaSuccess) return sfail(e, "mpcgpu_b200_solver_solve_host: " #x); } while (0)
     for (uint32_t ci = 0; ci < nchunks; ci++) {
         const int b = ci % NBUF;
         const size_t first = (size_t)ci * S->chunk;

@@ -42,6 +42,10 @@ SQPB = os.path.join(RUN, "sqp_batched_check")   # tools/sqp_batched_check.cu
 KKTB = os.path.join(RUN, "kkt_batched_check")   # tools/kkt_batched_check.cu
 SLOT = os.path.join(RUN, "track_slot_%s_n%d")    # tools/track_slot.cu: simulateMPC over the pcg / b200 slot
 SLOTAB = os.path.join(RUN, "slot_ab_n%d")        # tools/slot_ab.cu: one SQP iteration of either slot on identical state
+# product-side executable that needs the reference's dynamics headers to build: tools/e2e_producer.cu (batched KKT
+# producer -> fused solve from host buffers).  NOT test infrastructure, so it is kept outside oracle/.
+PLUGINS = os.path.join(os.path.dirname(HERE), "mpcgpu_b200", "_plugins")
+E2EP = os.path.join(PLUGINS, "e2e_producer")
 
 
 def _ref_nvcc(src, out, defs=(), link_product=False):
@@ -54,7 +58,8 @@ def _ref_nvcc(src, out, defs=(), link_product=False):
     cmd = [NVCC, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-w", "-lineinfo"]
     cmd += list(defs) + [a for i in inc for a in ("-I", i)] + [src, "-o", out, "-lcublas"]
     if link_product:   # the L2 slot calls the C ABI of mpcgpu_b200/libmpcgpu_b200.so
-        cmd += ["-L", os.path.join(root, "mpcgpu_b200"), "-lmpcgpu_b200", "-Xlinker", "-rpath=$ORIGIN/../../../mpcgpu_b200"]
+        rpath = "$ORIGIN/.." if link_product == "plugin" else "$ORIGIN/../../../mpcgpu_b200"
+        cmd += ["-L", os.path.join(root, "mpcgpu_b200"), "-lmpcgpu_b200", "-Xlinker", "-rpath=" + rpath]
     _run(cmd)
 
 
@@ -101,6 +106,15 @@ def _build_reference_cuda(force, verbose):
     for n in TRACK_KNOTS:
         if os.path.exists(lib) and (force or _stale(SLOTAB % n, slot_deps + [ab_src])):
             jobs.append((ab_src, SLOTAB % n, ["-DKNOT_POINTS=%d" % n, "-DSQP_MAX_TIME_US=100000000"], True))
+    ep_src = os.path.join(root, "tools", "e2e_producer.cu")
+    ep_deps = deps + [ep_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "kkt_batched.cuh"), os.path.join(root, "include", "mpcgpu_b200.h")]
+    if os.path.exists(lib) and (force or _stale(E2EP, ep_deps)):
+        os.makedirs(os.path.join(PLUGINS, "examples", "trajfiles"), exist_ok=True)
+        for f in ("0_0_eepos.traj", "0_0_traj.csv"):
+            dst = os.path.join(PLUGINS, "examples", "trajfiles", f)
+            if not os.path.exists(dst):
+                shutil.copyfile(os.path.join(REF, "examples", "trajfiles", f), dst)
+        jobs.append((ep_src, E2EP, [], "plugin"))
     kb_src = os.path.join(root, "tools", "kkt_batched_check.cu")     # batched KKT producer vs the reference kernel
     kb_deps = deps + [kb_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "kkt_batched.cuh"),
                       os.path.join(root, "include", "mpcgpu_b200.h")]

@@ -108,23 +108,81 @@ def test_shim_pcg_launched_like_the_reference_slot(N, tol, tmp_path):
     assert rel(lam_g, lam_s) < max(1e-4, 3.0 * oracle.pcg_noise_floor(S, N, S32, P32, g32, lam0, it_g))
 
 
-def test_closed_loop_tracking_through_the_b200_slot():
-    """The reference's unchanged simulateMPC (include/mpcsim.cuh) with its solver call bound to
-    mpcgpu_b200/shim/b200/sqp.cuh (tools/track_slot.cu): the IIWA arm must keep tracking the 0_0
-    figure-eight, every control step must get at least the SQP iterations the PCG slot gets."""
+def _track(exe_name, tol, env_extra=None):
     import json
-    exe = os.path.join(RUN, "track_slot_b200_n32")
+    exe = os.path.join(RUN, exe_name)
     if not os.path.exists(exe):
-        pytest.fail("oracle/_ref/run/track_slot_b200_n32 missing: run oracle/build.py where /root/reference exists")
+        pytest.fail("oracle/_ref/run/%s missing: run oracle/build.py where /root/reference exists" % exe_name)
     env = dict(os.environ)
     env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
-    r = subprocess.run([exe, "5e-6"], cwd=RUN, env=env, capture_output=True, text=True, timeout=300)
+    env.update(env_extra or {})
+    r = subprocess.run([exe, str(tol)], cwd=RUN, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (exe_name, r.stdout[-400:], r.stderr[-400:])
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    keep = os.path.join(ROOT, "gpurun_out")
+    if os.path.isdir(keep):
+        with open(os.path.join(keep, "closed_loop_tests.jsonl"), "a") as f:
+            f.write(json.dumps(dict(out, exe=exe_name, env=env_extra or {})) + "\n")
+    return out
+
+
+@pytest.mark.parametrize("N,tol", [(32, 5e-6), (128, 1e-4)])
+def test_closed_loop_tracking_through_the_slots(N, tol):
+    """The reference's unchanged simulateMPC (include/mpcsim.cuh, 2 ms SQP budget per control step, 0_0 figure
+    eight; tools/track_slot.cu) over four bindings of its solver slot, same box, same run:
+      ref   include/pcg/sqp.cuh with the reference's OWN form_schur_system kernel + the shim's pcg (round-1 L1)
+      l1    include/pcg/sqp.cuh on the whole L1 shim (stage 1 bound to mpcb200::schur_kernel as well)
+      b200  mpcgpu_b200/shim/b200/sqp.cuh (fused solve, graphed iteration), uncapped
+      cap   b200 limited to the SQP iterations per step the reference slot reaches (MPCGPU_B200_SLOT_MAX_SQP)
+    Measured (profiles/r2a_track_capped.jsonl): at N = 32 the tracking error of THIS MPC formulation grows with the
+    SQP iterations spent per control step (0.075 / 0.104 / 0.114 / 0.118 at 2 / 4 / 8 / 16 iterations) whichever
+    slot runs them, so the slots are compared at EQUAL iteration budget, and the uncapped run only against the
+    measured trend."""
+    import math
+    ref = _track("track_slot_pcgrefschur_n%d" % N, tol)
+    l1 = _track("track_slot_pcg_n%d" % N, tol)
+    b = _track("track_slot_b200_n%d" % N, tol)
+    cap = max(1, int(math.ceil(ref["sqp_iters_mean"])))
+    bc = _track("track_slot_b200_n%d" % N, tol, {"MPCGPU_B200_SLOT_MAX_SQP": str(cap)})
+    for o in (ref, l1, b, bc):
+        assert o["control_steps"] > 1000 and np.isfinite(o["tracking_err_mean"])
+    # same iteration budget -> the b200 slot tracks at least as well as the reference slot (it completes every
+    # iteration it starts; the reference slot's budget often expires between its stages)
+    assert bc["sqp_iters_mean"] <= cap + 1e-6
+    assert bc["tracking_err_mean"] <= 1.25 * ref["tracking_err_mean"], (bc, ref)
+    # the slot's purpose: several times the reference slot's SQP iterations inside the same 2 ms
+    assert b["sqp_iters_mean"] >= 2.0 * ref["sqp_iters_mean"], (b, ref)
+    assert l1["sqp_iters_mean"] >= 0.9 * ref["sqp_iters_mean"], (l1, ref)
+    assert l1["tracking_err_mean"] <= 1.35 * ref["tracking_err_mean"], (l1, ref)
+    if N >= 128:
+        assert b["tracking_err_mean"] <= 1.10 * ref["tracking_err_mean"], (b, ref)     # measured 0.058-0.064 vs 0.078
+    else:
+        assert b["tracking_err_mean"] <= 1.35 * ref["tracking_err_mean"], (b, ref)     # measured 0.118 vs 0.098 (see docstring)
+
+
+@pytest.mark.parametrize("N,tol", [(32, 5e-6), (128, 1e-4)])
+def test_one_sqp_iteration_of_either_slot_on_identical_state(N, tol):
+    """tools/slot_ab.cu: ONE SQP iteration of the reference's unchanged PCG slot (its own Schur kernel, its compute_dz,
+    its line search, cuBLAS update) against ONE iteration of the b200 slot from identical (xu, lambda0, rho), 6 chained
+    iterations on 4 windows of the 0_0 trajectory (warm lambda, adapting rho): same line-search decision and rho every
+    time, PCG iteration counts within +-1 (one near-threshold exception allowed per 24), the applied step alpha dz
+    within the fp32 floor of the window (median <= 1e-3)."""
+    import json
+    exe = os.path.join(RUN, "slot_ab_n%d" % N)
+    if not os.path.exists(exe):
+        pytest.fail("oracle/_ref/run/slot_ab_n%d missing: run oracle/build.py where /root/reference exists" % N)
+    env = dict(os.environ)
+    env["LD_LIBRARY_PATH"] = "/usr/local/cuda/lib64:" + env.get("LD_LIBRARY_PATH", "")
+    r = subprocess.run([exe, str(tol), "6"], cwd=RUN, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-400:], r.stderr[-400:])
     out = json.loads(r.stdout.strip().splitlines()[-1])
-    assert out["control_steps"] > 1000
-    assert out["sqp_iters_mean"] >= 3.0            # PCG slot on the same box: 3.8 (profiles/r1_track_slot.jsonl)
-    assert np.isfinite(out["tracking_err_mean"]) and out["tracking_err_mean"] < 0.25   # PCG slot: 0.10
-    assert out["final_tracking_err"] < 0.25
+    n = out["sqp_iterations_compared"]
+    assert n == 24
+    assert out["same_rho"] == n and out["same_accept_decision"] == n
+    assert out["pcg_iters_within_1"] >= n - 1 and out["max_pcg_iter_diff"] <= 4
+    steps = [p["step_rel"] for p in out["per_iteration"] if p["accepted"] == [1, 1]]
+    assert out["same_step_length"] >= out["accepted_steps"] - 1          # a near-tie of two merits may pick the other length
+    assert float(np.median(steps)) <= 1e-3 and float(np.median([p["lambda_rel"] for p in out["per_iteration"]])) <= 1e-3
 
 
 @pytest.mark.parametrize("N,B", [(8, 5), (32, 40), (64, 300), (128, 64)])

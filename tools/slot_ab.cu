@@ -80,7 +80,7 @@ int main(int argc, char** argv) {
     cfg.pcg_block = PCG_NUM_THREADS; cfg.pcg_exit_tol = tol; cfg.pcg_max_iter = PCG_MAX_ITER;
 
     double worst_lam = 0, worst_step = 0, worst_xu = 0;
-    int n_iter = 0, n_iters_pm1 = 0, n_same_rho = 0, n_same_accept = 0, max_iter_diff = 0, n_accepted = 0;
+    int n_iter = 0, n_iters_pm1 = 0, n_same_rho = 0, n_same_accept = 0, max_iter_diff = 0, n_accepted = 0, n_same_len = 0;
     std::string per = "[";
     for (uint32_t row0 : {0u, 100u, 200u, 300u}) {
         std::vector<float> h_ee, h_xu;
@@ -110,6 +110,9 @@ int main(int argc, char** argv) {
             n_iter++;
             n_iters_pm1 += std::abs(ia - ib) <= 1; max_iter_diff = std::max(max_iter_diff, std::abs(ia - ib));
             n_same_rho += rhoA == rhoB; n_same_accept += accA == accB; n_accepted += accA;
+            // the step length alpha is one of 1, 1/2, ..., 1/128: the same one iff the two steps have (nearly) the same norm
+            const bool same_len = accA && accB && std::fabs(std::sqrt(nB / nA) - 1.0) < 0.2;
+            n_same_len += same_len;
             worst_lam = std::max(worst_lam, dl); worst_step = std::max(worst_step, dst); worst_xu = std::max(worst_xu, dxu);
             char buf[256];
             snprintf(buf, sizeof buf, "%s{\"row0\": %u, \"it\": %d, \"pcg_iters\": [%d, %d], \"rho\": [%g, %g], \"accepted\": [%d, %d], "
@@ -122,8 +125,8 @@ int main(int argc, char** argv) {
     }
     per += "]";
     printf("{\"knot_points\": %u, \"pcg_exit_tol\": %g, \"sqp_iterations_compared\": %d, \"pcg_iters_within_1\": %d, "
-           "\"max_pcg_iter_diff\": %d, \"same_rho\": %d, \"same_accept_decision\": %d, \"accepted_steps\": %d, "
+           "\"max_pcg_iter_diff\": %d, \"same_rho\": %d, \"same_accept_decision\": %d, \"accepted_steps\": %d, \"same_step_length\": %d, "
            "\"lambda_rel_max\": %.4g, \"step_rel_max\": %.4g, \"xu_rel_max\": %.4g, \"per_iteration\": %s}\n",
-           N, tol, n_iter, n_iters_pm1, max_iter_diff, n_same_rho, n_same_accept, n_accepted, worst_lam, worst_step, worst_xu, per.c_str());
+           N, tol, n_iter, n_iters_pm1, max_iter_diff, n_same_rho, n_same_accept, n_accepted, n_same_len, worst_lam, worst_step, worst_xu, per.c_str());
     return 0;
 }
