@@ -31,15 +31,8 @@
 
 namespace mpcb200 {
 
-#ifndef MPCB200_TM_WPC
-#define MPCB200_TM_WPC 1
-#endif
 #ifndef MPCB200_PINV_TMEM
 #define MPCB200_PINV_TMEM 1   // 0: Pinv rows stay in shared memory during the PCG phase (A/B builds)
-#endif
-#ifndef MPCB200_TM_BALANCED
-#define MPCB200_TM_BALANCED 1 // 1: registers hold Sl, Sd, Pd and tensor memory Sr, Pl, Pr (each matvec streams <= 2 of its 3
-                              //    blocks from tensor memory); 0: S in registers, all of Pinv in tensor memory (round 1)
 #endif
 #ifndef MPCB200_PCG_VARIANT
 #define MPCB200_PCG_VARIANT 0 // default iteration of pcg_rows: 0 = the reference's two-reduction PCG, 1 = single-reduction PCG
@@ -59,7 +52,6 @@ struct Cfg {
     using T2 = typename Num<T_>::T2;
     static constexpr bool F32 = sizeof(T_) == 4;
     static constexpr bool TM = TM_ != 0 && F32;
-    static constexpr bool TMB = TM && MPCB200_TM_BALANCED != 0;
     static constexpr int S = 14, C = 7;
     static constexpr int KPC = KPC_, CL = CL_;
     static constexpr int LPK = LPK_;            // lanes per knot
@@ -86,11 +78,9 @@ struct Cfg {
     static constexpr int oMb = oRed + 2 * NREDP;        // 2 mbarriers (8 B each), cluster kernels
     static constexpr int oTm = oMb + 4;                 // TMEM base address of this CTA (+ pad)
     static constexpr int FLOATS = oTm + 4;
-    // tensor-memory copy of Pinv: per lane 3 parts x 7 column pairs x RPT rows, in chunks of 2*RPT floats
-    static constexpr int TWPC = MPCB200_TM_WPC;         // column pairs per chunk
-    static constexpr int TCH = 2 * RPT * TWPC;          // floats per tcgen05.ld (x4 / x8 / x16)
-    static constexpr int TNCH = (21 + TWPC - 1) / TWPC; // chunks per matvec
-    static constexpr int TPT = TNCH * TCH;              // columns per thread
+    // tensor-memory copy of Sr | Pl | Pr: per lane 7 chunks of 2*RPT columns (Sr pair w of my RPT rows) and 7 chunks of
+    // 4*RPT (Pl pair w | Pr pair w)
+    static constexpr int TPT = 42 * RPT;                // columns per thread
     static constexpr int TCOLS = pow2_at_least(((NW + 3) / 4) * TPT);   // allocation, power of two <= 512
     static_assert(!TM || TCOLS <= 512, "tensor memory has 512 columns");
     static constexpr size_t SMEM_BYTES = sizeof(T) * FLOATS;
@@ -887,7 +877,6 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     if (CL > 1 && tid == 0) { mbar_init(mb, 1); mbar_init(mb + 1, 1); fence_mbar_init_cluster(); }
     const T* myP = smem + CF::oP + sl * PK;
     constexpr bool TM = CF::TM;
-    constexpr int TCH = CF::TCH;
     uint32_t* tm_word = reinterpret_cast<uint32_t*>(smem + CF::oTm);
     uint32_t tcol = 0;      // TMEM address of this lane's first column
     if (TM) {               // published by the barriers below, long before the first use
@@ -895,153 +884,93 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         tmem_fence_before_sync();
     }
 
-    // Balanced operand stores (TMB): registers hold Sl, Sd (R) and Pd (below), tensor memory holds Sr | Pl | Pr as
-    // 7 chunks of 2*RPT columns (column pair w of my RPT rows of Sr) followed by 7 chunks of 4*RPT (Pl pair w |
-    // Pr pair w).  The tensor-memory read path delivers ~1/4 of what the FFMA2 pipe can consume, so a matvec that
-    // streams all three of its blocks from it (round 1: Pinv) is bound by that path, and one that streams none
-    // leaves it idle; with one block of S and two of Pinv there, both matvecs sit near the FFMA2 floor.  Every
-    // accumulation chain keeps its order, so the bits are those of the all-register / all-TMEM forms.
-    constexpr bool TMB = CF::TMB;
-    T2 Pd[TMB ? RPT : 1][7];
-    auto s_mv_tm = [&](const T* vec, T (&y)[RPT]) {
-      if constexpr (TMB) {
-        TmemChunk<2 * RPT> buf[2];
-        buf[0].ld(tcol);
+    // The two block-row matvecs of an iteration.  ONE accumulation order everywhere (registers, shared memory, tensor
+    // memory, float or double), so every storage variant of a tiling gives the same bits: per row a single pair-wise
+    // accumulator runs over the column pairs w = 0..6 and, for each w, over the blocks left -> diagonal -> right
+    // (the oracle's bdmv is the same sum row by row); the two halves of the pair are added at the end.  One chain per
+    // row instead of one per block saves two of the three horizontal sums (round 1: 5 FADD per row and matvec; the
+    // FP32 pipe, not the issue slots, bounds this loop -- see DESIGN.md): 4 rows per lane and 2 warps per scheduler
+    // still cover the FFMA2 latency.
+    //
+    // Tensor-memory tilings (TM): registers hold Sl, Sd (R) and Pd (below); tensor memory holds Sr | Pl | Pr as 7 chunks
+    // of 2*RPT columns (column pair w of my RPT rows of Sr) followed by 7 chunks of 4*RPT (Pl pair w | Pr pair w),
+    // streamed one chunk ahead of the FFMA2s (tcgen05.wait::ld covers every load in flight: wait, THEN start the next).
+    // The tensor-memory read path delivers ~1/4 of what the FFMA2 pipe can consume: with one block of S and two of Pinv
+    // there (round 1: all of Pinv, none of S) neither matvec is bound by it.
+    T2 Pd[TM ? RPT : 1][7];
+    auto s_mv = [&](const T* vec, T (&y)[RPT]) {
         const T2* vl = reinterpret_cast<const T2*>(vec + (sl - 1) * VK);
         const T2* vd = reinterpret_cast<const T2*>(vec + sl * VK);
         const T2* vr = reinterpret_cast<const T2*>(vec + (sl + 1) * VK);
-        T2 al[RPT], ad[RPT], ar[RPT];
+        T2 acc[RPT];
 #pragma unroll
-        for (int j = 0; j < RPT; j++) { al[j] = splat(T(0)); ad[j] = splat(T(0)); ar[j] = splat(T(0)); }
-#pragma unroll
-        for (int w = 0; w < 7; w++) {
-            const T2 xl = vl[w], xd = vd[w], xr = vr[w];
-#pragma unroll
-            for (int j = 0; j < RPT; j++) { al[j] = fma2(R.Sl[j][w], xl, al[j]); ad[j] = fma2(R.Sd[j][w], xd, ad[j]); }
-            buf[w & 1].wait();          // tcgen05.wait::ld covers every load in flight: wait, THEN start the next
-            if (w + 1 < 7) buf[(w + 1) & 1].ld(tcol + (w + 1) * 2 * RPT);
-#pragma unroll
-            for (int j = 0; j < RPT; j++)
-                ar[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * j]), __uint_as_float(buf[w & 1].q[2 * j + 1])), xr, ar[j]);
-        }
-#pragma unroll
-        for (int j = 0; j < RPT; j++) y[j] = (hsum(al[j]) + hsum(ad[j])) + hsum(ar[j]);
-      }
-    };
-    auto p_mv_tmb = [&](const T* vec, T (&y)[RPT]) {
-      if constexpr (TMB) {
-        TmemChunk<4 * RPT> buf[2];
-        const uint32_t base = tcol + 7 * 2 * RPT;
-        buf[0].ld(base);
-        const T2* vl = reinterpret_cast<const T2*>(vec + (sl - 1) * VK);
-        const T2* vd = reinterpret_cast<const T2*>(vec + sl * VK);
-        const T2* vr = reinterpret_cast<const T2*>(vec + (sl + 1) * VK);
-        T2 a0[RPT], a1[RPT], a2[RPT];
-#pragma unroll
-        for (int j = 0; j < RPT; j++) { a0[j] = splat(T(0)); a1[j] = splat(T(0)); a2[j] = splat(T(0)); }
-#pragma unroll
-        for (int w = 0; w < 7; w++) {
-            const T2 xl = vl[w], xd = vd[w], xr = vr[w];
-#pragma unroll
-            for (int j = 0; j < RPT; j++) a0[j] = fma2(Pd[j][w], xd, a0[j]);
-            buf[w & 1].wait();
-            if (w + 1 < 7) buf[(w + 1) & 1].ld(base + (w + 1) * 4 * RPT);
-#pragma unroll
-            for (int j = 0; j < RPT; j++) {
-                a1[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * j]), __uint_as_float(buf[w & 1].q[2 * j + 1])), xl, a1[j]);
-                a2[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * RPT + 2 * j]), __uint_as_float(buf[w & 1].q[2 * RPT + 2 * j + 1])), xr, a2[j]);
-            }
-        }
-#pragma unroll
-        for (int j = 0; j < RPT; j++) y[j] = rm.ok[j] ? (hsum(a1[j]) + hsum(a0[j])) + hsum(a2[j]) : T(0);
-      }
-    };
-    // y(rows) = [L D R] . [x_{k-1}; x_k; x_{k+1}], S rows from registers
-    auto s_mv_reg = [&](const T* vec, T (&y)[RPT]) {
-        T2 xl[7], xd[7], xr[7];
-        ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
-#pragma unroll
-        for (int j = 0; j < RPT; j++) {
-            const T2 a = dot14_acc(R.Sl[j], xl, splat(T(0))), b = dot14_acc(R.Sd[j], xd, splat(T(0))),
-                         c = dot14_acc(R.Sr[j], xr, splat(T(0)));
-            y[j] = (hsum(a) + hsum(b)) + hsum(c);
-        }
-    };
-    // same with the Pinv rows from shared memory (row = [Pd | Pl | Pr | pad])
-    auto p_mv = [&](const T* vec, T (&y)[RPT]) {
-        T2 xl[7], xd[7], xr[7];
-        ld14_v4(xl, vec + (sl - 1) * VK); ld14_v4(xd, vec + sl * VK); ld14_v4(xr, vec + (sl + 1) * VK);
-#pragma unroll
-        for (int j = 0; j < RPT; j++) {
-            T2 acc[3] = {splat(T(0)), splat(T(0)), splat(T(0))};
-            if constexpr (CF::F32) {
-                const float4* q4 = reinterpret_cast<const float4*>(myP + rm.row[j] * PR);
-#pragma unroll
-                for (int q = 0; q < 11; q++) {
-                    const float4 u = q4[q];
-                    // floats 4q .. 4q+3 of the row: pairs 2q, 2q+1 of 21 (Pd 0-6, Pl 7-13, Pr 14-20)
-#pragma unroll
-                    for (int h = 0; h < 2; h++) {
-                        const int pi = 2 * q + h;
-                        if (pi < 21) {
-                            const int part = pi / 7, w = pi % 7;
-                            const T2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
-                            acc[part] = fma2(h ? f2(u.z, u.w) : f2(u.x, u.y), x, acc[part]);
-                        }
-                    }
-                }
-            } else {   // doubles: one pair per 16 B load, same order
-                const T2* q2 = reinterpret_cast<const T2*>(myP + rm.row[j] * PR);
-#pragma unroll
-                for (int pi = 0; pi < 21; pi++) {
-                    const int part = pi / 7, w = pi % 7;
-                    const T2 x = (part == 0) ? xd[w] : (part == 1) ? xl[w] : xr[w];
-                    acc[part] = fma2(q2[pi], x, acc[part]);
-                }
-            }
-            y[j] = rm.ok[j] ? (hsum(acc[1]) + hsum(acc[0])) + hsum(acc[2]) : T(0);
-        }
-    };
-    // same rows from tensor memory: chunk (part, w) = column pair w of all my RPT rows of block `part`
-    // (0 Pd, 1 Pl, 2 Pr); the accumulation order per row is the one of p_mv -> identical bits.
-    // Loads run one chunk ahead of the FFMA2s; shared memory only delivers the three x vectors.
-    auto p_mv_tm = [&](const T* vec, T (&y)[RPT]) {
-      if constexpr (TM) {
-        constexpr int WPC = CF::TWPC, NCH = CF::TNCH;
-        TmemChunk<TCH> buf[2];
-        T part_sum[RPT];
-        buf[0].ld(tcol);
-#pragma unroll
-        for (int part = 0; part < 3; part++) {
-            T2 x[7];
-            ld14_v4(x, vec + (sl + (part == 0 ? 0 : (part == 1 ? -1 : 1))) * VK);
-            T2 acc[RPT];
-#pragma unroll
-            for (int j = 0; j < RPT; j++) acc[j] = splat(T(0));
+        for (int j = 0; j < RPT; j++) acc[j] = splat(T(0));
+        if constexpr (TM) {
+            TmemChunk<2 * RPT> buf[2];
+            buf[0].ld(tcol);
 #pragma unroll
             for (int w = 0; w < 7; w++) {
-                const int pi = part * 7 + w, c = pi / WPC, o = (pi % WPC) * 2 * RPT;
-                if (pi % WPC == 0) {     // tcgen05.wait::ld covers every load in flight: wait, THEN start the next
-                    buf[c & 1].wait();
-                    if (c + 1 < NCH) buf[(c + 1) & 1].ld(tcol + (c + 1) * TCH);
-                }
+                const T2 xl = vl[w], xd = vd[w], xr = vr[w];
+#pragma unroll
+                for (int j = 0; j < RPT; j++) { acc[j] = fma2(R.Sl[j][w], xl, acc[j]); acc[j] = fma2(R.Sd[j][w], xd, acc[j]); }
+                buf[w & 1].wait();
+                if (w + 1 < 7) buf[(w + 1) & 1].ld(tcol + (w + 1) * 2 * RPT);
 #pragma unroll
                 for (int j = 0; j < RPT; j++)
-                    acc[j] = fma2(f2(__uint_as_float(buf[c & 1].q[o + 2 * j]), __uint_as_float(buf[c & 1].q[o + 2 * j + 1])), x[w], acc[j]);
+                    acc[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * j]), __uint_as_float(buf[w & 1].q[2 * j + 1])), xr, acc[j]);
             }
+        } else {
 #pragma unroll
-            for (int j = 0; j < RPT; j++) {
-                if (part == 0) part_sum[j] = hsum(acc[j]);
-                else if (part == 1) part_sum[j] = hsum(acc[j]) + part_sum[j];
-                else y[j] = rm.ok[j] ? part_sum[j] + hsum(acc[j]) : T(0);
+            for (int w = 0; w < 7; w++) {
+                const T2 xl = vl[w], xd = vd[w], xr = vr[w];
+#pragma unroll
+                for (int j = 0; j < RPT; j++) {
+                    acc[j] = fma2(R.Sl[j][w], xl, acc[j]); acc[j] = fma2(R.Sd[j][w], xd, acc[j]); acc[j] = fma2(R.Sr[j][w], xr, acc[j]);
+                }
             }
         }
-      }
+#pragma unroll
+        for (int j = 0; j < RPT; j++) y[j] = hsum(acc[j]);
     };
     auto pinv_mv = [&](const T* vec, T (&y)[RPT]) {
-        if constexpr (TMB) p_mv_tmb(vec, y); else if constexpr (TM) p_mv_tm(vec, y); else p_mv(vec, y);
+        const T2* vl = reinterpret_cast<const T2*>(vec + (sl - 1) * VK);
+        const T2* vd = reinterpret_cast<const T2*>(vec + sl * VK);
+        const T2* vr = reinterpret_cast<const T2*>(vec + (sl + 1) * VK);
+        T2 acc[RPT];
+#pragma unroll
+        for (int j = 0; j < RPT; j++) acc[j] = splat(T(0));
+        if constexpr (TM) {
+            TmemChunk<4 * RPT> buf[2];
+            const uint32_t base = tcol + 7 * 2 * RPT;
+            buf[0].ld(base);
+#pragma unroll
+            for (int w = 0; w < 7; w++) {
+                const T2 xl = vl[w], xd = vd[w], xr = vr[w];
+                buf[w & 1].wait();
+                if (w + 1 < 7) buf[(w + 1) & 1].ld(base + (w + 1) * 4 * RPT);
+#pragma unroll
+                for (int j = 0; j < RPT; j++) {
+                    acc[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * j]), __uint_as_float(buf[w & 1].q[2 * j + 1])), xl, acc[j]);
+                    acc[j] = fma2(Pd[j][w], xd, acc[j]);
+                    acc[j] = fma2(f2(__uint_as_float(buf[w & 1].q[2 * RPT + 2 * j]), __uint_as_float(buf[w & 1].q[2 * RPT + 2 * j + 1])), xr, acc[j]);
+                }
+            }
+        } else {      // the Pinv rows from shared memory (row = [Pd | Pl | Pr | pad]), same order
+#pragma unroll
+            for (int w = 0; w < 7; w++) {
+                const T2 xl = vl[w], xd = vd[w], xr = vr[w];
+#pragma unroll
+                for (int j = 0; j < RPT; j++) {
+                    const T* row = myP + rm.row[j] * PR;
+                    acc[j] = fma2(*reinterpret_cast<const T2*>(row + CF::cL + 2 * w), xl, acc[j]);
+                    acc[j] = fma2(*reinterpret_cast<const T2*>(row + CF::cD + 2 * w), xd, acc[j]);
+                    acc[j] = fma2(*reinterpret_cast<const T2*>(row + CF::cR + 2 * w), xr, acc[j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RPT; j++) y[j] = rm.ok[j] ? hsum(acc[j]) : T(0);
     };
-    auto s_mv = [&](const T* vec, T (&y)[RPT]) { if constexpr (TMB) s_mv_tm(vec, y); else s_mv_reg(vec, y); };
     auto put = [&](T* dst, const T (&v)[RPT]) {        // my rows of a 16-T vector slot
 #pragma unroll
         for (int j = 0; j < RPT; j++) if (rm.ok[j]) dst[rm.row[j]] = v[j];
@@ -1115,7 +1044,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         gpull_rows(2, tg0, hl_p, hr_p);
     }
     __syncthreads();
-    if constexpr (TMB) {   // my PROW rows are final (schur_rows / load_rows ended on a barrier): Sr, Pl, Pr -> tensor memory, Pd -> registers
+    if constexpr (TM) {   // my PROW rows are final (schur_rows / load_rows ended on a barrier): Sr, Pl, Pr -> tensor memory, Pd -> registers
         tmem_fence_after_sync();
         const int warp = tid >> 5;
         tcol = *tm_word + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * CF::TPT);
@@ -1146,28 +1075,6 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     if (SPLIT) gpull_rows(3, tg0, hl_r, hr_r);
     cluster_sync_all<CL>();
 
-    if constexpr (TM && !TMB) {   // PROW is final (barrier above): move my Pinv rows into tensor memory
-        tmem_fence_after_sync();
-        const int warp = tid >> 5;
-        tcol = *tm_word + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)((warp >> 2) * CF::TPT);
-#pragma unroll
-        for (int c = 0; c < CF::TNCH; c++) {
-            TmemChunk<TCH> ch;
-#pragma unroll
-            for (int u = 0; u < CF::TWPC; u++) {
-                const int pi = c * CF::TWPC + u, part = pi / 7, w = pi % 7;
-                const int colofs = (part == 0 ? CF::cD : (part == 1 ? CF::cL : CF::cR)) + 2 * w;
-#pragma unroll
-                for (int j = 0; j < RPT; j++) {
-                    T2 v = f2(T(0), T(0));
-                    if (pi < 21) v = *reinterpret_cast<const T2*>(myP + rm.row[j] * PR + colofs);
-                    ch.q[u * 2 * RPT + 2 * j] = __float_as_uint(v.x); ch.q[u * 2 * RPT + 2 * j + 1] = __float_as_uint(v.y);
-                }
-            }
-            ch.st(tcol + c * TCH);
-        }
-        tmem_wait_st();
-    }
     unsigned iter = 0;
     bool max_iter_exit = true;
     if constexpr (VAR == 1) {

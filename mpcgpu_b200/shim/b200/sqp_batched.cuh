@@ -24,6 +24,7 @@
 // decides how many iterations to enqueue).
 #pragma once
 #include <cstdint>
+#include <type_traits>
 #include <vector>
 #include <cuda_runtime.h>
 #include <cooperative_groups.h>
@@ -47,7 +48,11 @@ struct BatchedSqpState {
     T* drho;         // its growth factor                   (include/pcg/sqp.cuh:96)
     T* merit;        // merit of the current iterate
     T* step;         // step length taken by the last iteration (0: none, rho raised instead)
-    uint32_t* flags; // bit 0: rho exceeded RHO_MAX and was reset (the reference leaves its loop there)
+    uint32_t* flags; // bit 0: rho exceeded RHO_MAX and was reset.  The reference LEAVES its SQP loop at that point
+                     // (include/pcg/sqp.cuh:379-383): from then on the instance is frozen here too -- select_step_batched
+                     // takes no further step and changes neither rho nor the merit (the batched linearise / solve / line
+                     // search kernels still compute for it: their results are ignored), until the caller clears the bit
+                     // (the reference's next sqpSolvePcg call starts again from rho_reset).
 };
 
 // Point merits J_k + mu c_k of (knot, step length p, instance): slot p < 8 evaluates xu + alpha_p dz like
@@ -120,7 +125,10 @@ __global__ void select_step_batched(uint32_t knot_points, uint32_t nz, T* d_poin
         if (threadIdx.x == 0) s_merit[p] = pm[0];
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x == 0 && (st.flags[b] & 1u)) {      // left the loop (rho ran away): frozen, like the reference's `break`
+        s_alpha = T(0);
+        st.step[b] = T(0);
+    } else if (threadIdx.x == 0) {
         const T merit_now = st.merit[b];
         uint32_t best = 0;
         T best_merit = merit_now;
@@ -159,6 +167,9 @@ struct BatchedSqp {
     BatchedSqpState<T> st{};
 
     cudaError_t create(uint32_t s_, uint32_t c_, uint32_t N_, uint32_t B_, T rho0) {
+        static_assert(std::is_same<T, float>::value, "BatchedSqp: the per-instance-rho solve exists in fp32 only "
+                                                     "(mpcgpu_b200_kkt_solve_dz_rhovec_f32); build with USE_DOUBLES 0");
+        if (B_ == 0 || B_ > 65535 || N_ < 2) return cudaErrorInvalidValue;     // the batch index is gridDim.y / gridDim.z
         s = s_; c = c_; N = N_; B = B_; nz = (s + c) * N - c;
         const size_t zG = (size_t)(s * s + c * c) * N - c * c, zC = (size_t)(s * s + s * c) * (N - 1);
         cudaError_t e;

@@ -94,21 +94,24 @@ def test_consecutive_solves_alternate_mailbox_halves_with_mixed_configs():
     mail = torch.zeros((world, mg.mailbox_bytes() // 4), dtype=torch.int32, device=DEV)
     ptrs = [mail[r].data_ptr() for r in range(world)]
     Sg, Pg, gam = dev(S32), dev(P32), dev(g32)
-    it = torch.zeros(world, dtype=torch.int32, device=DEV); ex = torch.zeros(world, dtype=torch.uint8, device=DEV)
     epoch, seen = 0, []
     for max_iter, tol in ((10000, 1e-4), (7, 1e-30), (10000, 1e-6), (50, 1e-4), (10000, 1e-4)):
         cfg = mg.PcgConfig(pcg_exit_tol=tol, pcg_max_iter=max_iter)
         assert mg.epoch_stride(cfg) % 2 == 1 and mg.epoch_stride(cfg) > 2 * max_iter + 8
         lam = torch.zeros(S * N, device=DEV)
+        it = torch.zeros(world, dtype=torch.int32, device=DEV); ex = torch.zeros(world, dtype=torch.uint8, device=DEV)
         mg.knotsplit_pcg(S, n, world, 0, world, epoch, ptrs, Sg, Pg, gam, lam, it, ex, cfg)   # queued back to back
-        seen.append((epoch & 1, lam, max_iter, tol))
+        seen.append((epoch & 1, lam, it, ex, max_iter, tol))
         epoch += mg.epoch_stride(cfg)
     torch.cuda.synchronize()
     assert [p for p, *_ in seen] == [0, 1, 0, 1, 0]
-    for _, lam, max_iter, tol in seen:
-        lam_o, it_o, _ = oracle.pcg(S, N, S32, P32, g32, np.zeros(S * N, np.float32), max_iter, tol)
-        lam_s, _, _ = oracle.pcg(S, N, S32, P32, g32, np.zeros(S * N, np.float32), it_o, 0.0)
-        assert rel(lam.cpu().numpy(), lam_s) < max(1e-4, 3.0 * oracle.pcg_noise_floor(S, N, S32, P32, g32, np.zeros(S * N, np.float32), it_o)) or max_iter < 100
+    l0 = np.zeros(S * N, np.float32)
+    for _, lam, it, ex, max_iter, tol in seen:
+        its = it.cpu().numpy()
+        lam_o, it_o, ex_o = oracle.pcg(S, N, S32, P32, g32, l0, max_iter, tol)
+        assert np.all(its == its[0]) and abs(int(its[0]) - it_o) <= 1 and np.all(ex.cpu().numpy() == int(ex_o)), (its, it_o)
+        lam_s, _, _ = oracle.pcg(S, N, S32, P32, g32, l0, int(its[0]), 0.0)
+        assert rel(lam.cpu().numpy(), lam_s) < max(1e-4, 3.0 * oracle.pcg_noise_floor(S, N, S32, P32, g32, l0, int(its[0])))
     assert mg.knotsplit_last_timeout() is None
 
 

