@@ -159,6 +159,21 @@ int mpcgpu_b200_pcg_refstyle_f32(uint32_t state_size, uint32_t knot_points, cons
                                  uint32_t max_iter, float exit_tol, uint32_t* d_iters,
                                  uint8_t* d_max_iter_exit, void* d_ws, void* stream);
 
+/* The same kernel for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The scratch (d_r, d_p, d_v_temp, d_eta_new_temp) lives in a file-scope device array of the library
+ * (mpcgpu_b200/csrc/noalloc.cu) sized for state_size == 14 and knot_points <= mpcgpu_b200_noalloc_max_knots() == 512
+ * (61 440 B, held by every GPU that loads the library until exit); other sizes are refused with
+ * cudaErrorInvalidValue and a message.  The call itself allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine).  All calls on a device share that array and it keeps the last call's contents (the kernel
+ * writes every element before reading it, nothing needs clearing): calls that OVERLAP on the same GPU race --
+ * keep them on one stream or serialise them. */
+uint32_t mpcgpu_b200_noalloc_max_knots(void);
+int mpcgpu_b200_pcg_refstyle_noalloc_f32(uint32_t state_size, uint32_t knot_points, const float* d_S,
+                                         const float* d_Pinv, const float* d_gamma, float* d_lambda,
+                                         uint32_t max_iter, float exit_tol, uint32_t* d_iters,
+                                         uint8_t* d_max_iter_exit, void* stream);
+
 /* ---- host-buffer solver object (the call a user of the reference's solver slot makes
  * when the KKT blocks live on the host, cf. the QDLDL slot's PCIe round trip
  * include/qdldl/sqp.cuh:268-273).  Owns persistent device buffers and streams; nothing is

@@ -9,7 +9,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 CFLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
           "-Xcompiler", "-fPIC"]
 LFLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-cudart", "shared"]
-SOURCES = ["capi.cu", "capi_lat.cu", "capi_f64.cu", "solver.cu"]
+SOURCES = ["capi.cu", "capi_lat.cu", "capi_f64.cu", "solver.cu", "noalloc.cu"]
 OBJDIR = os.path.join(HERE, "_obj")
 
 
