@@ -338,18 +338,27 @@ def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, grp, reps=30, che
            "us_per_iter": float(tt[0]) / max(iters, 1), "max_iter_exit": int(ex.item()),
            "exchange": "tagged 8-byte NVLink peer stores into per-GPU mailboxes, polled locally; no NCCL in the solve"}
     if check:
-        parts = [torch.zeros_like(lam) for _ in range(world)]
-        dist.all_gather(parts, lam)
+        def gather(x):
+            parts = [torch.zeros_like(x) for _ in range(world)]
+            dist.all_gather(parts, x)
+            return torch.cat(parts).cpu().numpy() if rank == 0 else None
+        lam_g, S_g, P_g, g_g = gather(lam), gather(Sl), gather(Pl), gather(gl)
         if rank == 0:
             import oracle
-            lam_g = torch.cat(parts).cpu().numpy()
-            S32, P32, g32, _ = oracle.schur(S, C, N, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], np.float32)
             l0 = np.zeros(S * N, np.float32)
-            _, it_o, _ = oracle.pcg(S, N, S32, P32, g32, l0, 10000, tol)
-            lam_s, _, _ = oracle.pcg(S, N, S32, P32, g32, l0, iters, 0.0)
+            # stage-wise: the oracle PCG on the SAME S / Pinv / gamma rows the GPUs solved (their own Schur formation)
+            _, it_o, _ = oracle.pcg(S, N, S_g, P_g, g_g, l0, 10000, tol)
+            lam_s, _, _ = oracle.pcg(S, N, S_g, P_g, g_g, l0, iters, 0.0)
+            floor = float(oracle.pcg_noise_floor(S, N, S_g, P_g, g_g, l0, iters))
+            relv = float(np.linalg.norm(lam_g - lam_s) / np.linalg.norm(lam_s))
+            # end to end (the oracle's own fp32 Schur formation: another rounding of S, amplified by kappa(S))
+            S32, P32, g32, _ = oracle.schur(S, C, N, d["G"][0], d["C"][0], d["g"][0], d["c"][0], d["rho"], np.float32)
+            lam_e, _, _ = oracle.pcg(S, N, S32, P32, g32, l0, iters, 0.0)
             out["parity"] = {"oracle_iters": it_o, "iters_within_1": bool(abs(iters - it_o) <= 1),
-                             "lambda_rel_vs_oracle_same_iters": float(np.linalg.norm(lam_g - lam_s) / np.linalg.norm(lam_s)),
-                             "fp32_floor": float(oracle.pcg_noise_floor(S, N, S32, P32, g32, l0, iters))}
+                             "lambda_rel_vs_oracle_same_rows_same_iters": relv, "fp32_floor": floor,
+                             "within_max_1e-4_3x_floor": bool(relv <= max(1e-4, 3.0 * floor)),
+                             "lambda_rel_vs_oracle_own_schur_rows": float(np.linalg.norm(lam_g - lam_e) / np.linalg.norm(lam_e)),
+                             "schur_rows_rel_vs_oracle": float(np.linalg.norm(S_g - S32) / np.linalg.norm(S32))}
     return out
 
 
@@ -390,6 +399,9 @@ def knotsplit_leg(torch, mg, dist, rank, world, dev, tol):
     try:
         grp = mg.KnotSplitGroup()
         out["mailbox_one_way_us"] = grp.pingpong_us()
+        out["note"] = ("exchange_floor = 2 one-way hops per PCG iteration (two exchanges); nccl_exchange = the same two "
+                       "exchanges as torch.distributed NCCL calls (all_reduce + batched send/recv of the 14-float halos), "
+                       "host-launched, no compute: the SURVEY 8(e) baseline")
         out["exchange_floor_us_per_iter"] = 2.0 * out["mailbox_one_way_us"]
         if 512 % world == 0 and 512 // world in (64, 128, 256):
             out["n512"] = knotsplit_bench(torch, mg, dist, rank, world, dev, 512, tol, grp)
