@@ -24,6 +24,7 @@ struct BatchArgsT {
     T* dz = nullptr; size_t sdz = 0;   // optional compute_dz epilogue (fused) / output of dz_kernel
     const T* rho_dev = nullptr;        // optional: rho read from device memory (launches replayed from a CUDA graph)
     size_t rho_stride = 0;             // 0: one rho for the batch; 1: rho_dev[b] per instance (batched SQP iterations)
+    int pf_dist = 0;                   // > 0: while instance b iterates, prefetch the inputs of instance b + pf_dist into L2
 };
 using BatchArgs = BatchArgsT<float>;
 
@@ -157,6 +158,25 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) pcg_kernel(BatchArgsT<ty
                  a.exits + b);
 }
 
+// The inputs (G, C, g, c, lambda0) of instance `b` -> L2 (prefetch.global.L2, one 128 B line per request).  With one CTA
+// per SM nothing overlaps an instance's input staging (an HBM round trip per batch of loads: 10 % of the fused kernel's
+// stall samples sat on it) with another instance's arithmetic; the 126 MB L2 holds the inputs of every instance that is
+// about to start (148 x 215 KB = 32 MB), so the CTA that is iterating asks for the inputs of the instance that will get
+// its SM next.  A hint only: no ordering, no correctness role.
+template <class CF>
+__device__ __forceinline__ void prefetch_inputs_l2(const BatchArgsT<typename CF::T>& a, long long b) {
+    using T = typename CF::T;
+    if (b >= a.batch) return;
+    auto pf = [&](const T* base, size_t elems) {
+        const char* p = reinterpret_cast<const char*>(base);
+        const size_t bytes = elems * sizeof(T);
+        for (size_t off = (size_t)threadIdx.x * 128; off < bytes; off += (size_t)CF::NT * 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p + off));
+    };
+    pf(a.G + b * a.sG, a.sG); pf(a.C + b * a.sC, a.sC); pf(a.g + b * a.sg, a.sg); pf(a.c + b * a.sc, a.sc);
+    pf(a.lambda + b * a.sv, a.sv);
+}
+
 template <class CF>
 __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgsT<typename CF::T> a) {
     extern __shared__ float4 smem4[];
@@ -166,6 +186,7 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgsT<
     KktPtrs<T> P{a.G + b * a.sG, a.C + b * a.sC, a.g + b * a.sg, a.c + b * a.sc};
     RowsOf<CF> R;
     schur_rows<CF>(smem, P, a.N, a.rho_dev ? __ldg(a.rho_dev + b * a.rho_stride) : a.rho, R);
+    if (CF::CL == 1 && a.pf_dist > 0) prefetch_inputs_l2<CF>(a, (long long)b + a.pf_dist);
     pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
                  a.exits + b);
     if (a.dz) {   // compute_dz epilogue: lambda and G^-1 were written by this cluster, read back through L2

@@ -2,6 +2,7 @@
 // capi_f64.cu): opts the kernel in to its shared-memory size (and to cluster sizes > 8) once per device,
 // then launches batch * CL CTAs as clusters of CL.
 #pragma once
+#include <cstdlib>
 #include <cstring>
 
 #include "capi_internal.h"
@@ -40,7 +41,21 @@ cudaError_t launch(const BatchArgsT<typename CF::T>& a, cudaStream_t st) {
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    e = cudaLaunchKernelEx(&cfg, kern, a);
+    BatchArgsT<typename CF::T> args = a;
+    if (KIND == K_FUSED && CF::CL == 1) {
+        // batches of more than one wave: instance b prefetches the inputs of instance b + (CTAs resident at once) into L2
+        static thread_local int resident = 0;
+        static const bool on = [] { const char* v = getenv("MPCGPU_B200_L2_PREFETCH"); return !(v && v[0] == '0'); }();
+        if (!resident) {
+            int sms = 0, per_sm = 0;
+            if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess &&
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, CF::NT, CF::SMEM_BYTES) == cudaSuccess)
+                resident = sms * (per_sm > 0 ? per_sm : 1);
+            else { cudaGetLastError(); resident = 148; }
+        }
+        if (on && a.batch > resident) args.pf_dist = resident;
+    }
+    e = cudaLaunchKernelEx(&cfg, kern, args);
     if (e == cudaSuccess) detail::count_launch();
     return e;
 }

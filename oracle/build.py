@@ -38,6 +38,10 @@ RUN = os.path.join(REFOUT, "run")            # working directory of the referenc
 HARNESS = os.path.join(RUN, "ref_harness")
 TRACK = os.path.join(RUN, "track_iiwa_pcg_n%d")
 TRACK_KNOTS = (32, 128)
+# the same unchanged source with the SQP wall-clock budget lifted (-DSQP_MAX_TIME_US, an #ifndef knob of the reference's
+# settings.cuh:173): under ncu every launch takes milliseconds and the 2 ms budget would end each SQP solve after its first
+# kernel, so the profiler's launch list is taken from this build
+TRACK_NOLIMIT = os.path.join(RUN, "track_iiwa_pcg_n128_nolimit")
 SQPB = os.path.join(RUN, "sqp_batched_check")   # tools/sqp_batched_check.cu
 KKTB = os.path.join(RUN, "kkt_batched_check")   # tools/kkt_batched_check.cu
 SLOT = os.path.join(RUN, "track_slot_%s_n%d")    # tools/track_slot.cu: simulateMPC over the pcg / b200 slot
@@ -88,6 +92,9 @@ def _build_reference_cuda(force, verbose):
     for n in TRACK_KNOTS:
         if force or _stale(TRACK % n, deps):
             jobs.append((os.path.join(REF, "examples", "track_iiwa_pcg.cu"), TRACK % n, ["-DKNOT_POINTS=%d" % n], False))
+    if force or _stale(TRACK_NOLIMIT, deps):
+        jobs.append((os.path.join(REF, "examples", "track_iiwa_pcg.cu"), TRACK_NOLIMIT,
+                     ["-DKNOT_POINTS=128", "-DSQP_MAX_TIME_US=100000000"], False))
     slot_src = os.path.join(root, "tools", "track_slot.cu")
     slot_deps = deps + [slot_src, os.path.join(root, "mpcgpu_b200", "shim", "b200", "sqp.cuh"),
                         os.path.join(root, "include", "mpcgpu_b200.h")]
