@@ -149,17 +149,21 @@ template <> struct TmemChunk<4> {
     }
 };
 
-__device__ __forceinline__ float warp_sum(float v) {
+// Sum over the warp, the same bits in every lane.  A radix-8 and a radix-4 exchange (7 + 3 INDEPENDENT shuffles) instead of
+// the five dependent levels of a butterfly: two shuffle latencies on the critical path instead of five (the PCG loops are
+// latency chains: measured ~29 cycles per level).  The additions are those of the butterfly over lane bits 0,1,2 | 3,4.
+template <class T>
+__device__ __forceinline__ T warp_sum_radix(T a) {
+    T s[8];
+    s[0] = a;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+    for (int j = 1; j < 8; j++) s[j] = __shfl_xor_sync(0xffffffffu, a, j);
+    const T b = ((s[0] + s[1]) + (s[2] + s[3])) + ((s[4] + s[5]) + (s[6] + s[7]));
+    const T u1 = __shfl_xor_sync(0xffffffffu, b, 8), u2 = __shfl_xor_sync(0xffffffffu, b, 16), u3 = __shfl_xor_sync(0xffffffffu, b, 24);
+    return (b + u1) + (u2 + u3);
 }
-
-__device__ __forceinline__ double warp_sum(double v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
-}
+__device__ __forceinline__ float warp_sum(float v) { return warp_sum_radix(v); }
+__device__ __forceinline__ double warp_sum(double v) { return warp_sum_radix(v); }
 
 // ---- row tiles ------------------------------------------------------------------------
 // write my row (D values, zero padded to a multiple of 4) to dst + row*ld

@@ -127,6 +127,23 @@ def pcg_cg1(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32)
     return lam, int(iters.value), bool(flag.value)
 
 
+def pcg_sprec(s, N, S, Pinv, gamma, lambda0, max_iter, exit_tol, dtype=np.float32):
+    """PCG with S p carried by a recurrence (oracle_pcg_sprec): the checker of the product's PCG variant 2.
+    Returns (lambda, iters, max_iter_exit)."""
+    suf, ct = _dt(dtype)
+    S = np.ascontiguousarray(S, dtype=dtype)
+    Pinv = np.ascontiguousarray(Pinv, dtype=dtype)
+    gamma = np.ascontiguousarray(gamma, dtype=dtype)
+    lam = np.array(lambda0, dtype=dtype, copy=True)
+    iters = ctypes.c_uint(0)
+    flag = ctypes.c_ubyte(0)
+    fn = getattr(_lib("oracle"), "oracle_pcg_sprec_" + suf)
+    fn.restype = None
+    fn(ctypes.c_int(s), ctypes.c_int(N), _p(S), _p(Pinv), _p(gamma), _p(lam),
+       ctypes.c_uint(max_iter), ct(exit_tol), ctypes.byref(iters), ctypes.byref(flag))
+    return lam, int(iters.value), bool(flag.value)
+
+
 def pcg_noise_floor(s, N, S32, P32, g32, lambda0, iters):
     """How far correct fp32 implementations of the SAME `iters` PCG iterations drift apart on
     this input: max of (plain-order fp32 vs alternate-order fp32) and (fp32 vs fp64), relative

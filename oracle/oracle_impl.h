@@ -350,7 +350,7 @@ void F(oracle_pcg_mode)(int s, int N, const REAL *S, const REAL *Pinv, const REA
  * available together, so that a parallel implementation pays ONE global reduction per
  * iteration instead of two:   p.Sp = u.Su - beta^2 (p.Sp)_old.
  * Exit test, iteration count and max_iter flag as oracle_pcg.  This is the checker of the
- * product's MPCGPU_B200_PCG_VARIANT=1 kernels; oracle_pcg stays the statement of the
+ * product's MPCB200_PCG_VARIANT=1 builds; oracle_pcg stays the statement of the
  * reference's iteration.
  * ------------------------------------------------------------------------- */
 void F(oracle_pcg_cg1)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,
@@ -390,6 +390,54 @@ void F(oracle_pcg_cg1)(int s, int N, const REAL *S, const REAL *Pinv, const REAL
         gam = F(dot)(n, r, u);
         del = F(dot)(n, u, w);
         if (FABS(gam) < exit_tol) { iter++; max_iter_exit = 0; break; }
+    }
+    *iters_out = iter;
+    *max_iter_exit_out = max_iter_exit;
+    free(r);
+}
+
+/* ---------------------------------------------------------------------------
+ * PCG with S p carried by a recurrence (product variant 2): the iteration of oracle_pcg with
+ * ONE substitution -- after rt = Pinv r the product S rt is formed (on the GPU: while the
+ * reduction of r.rt is in flight, which is the point) and
+ *     p <- rt + beta p ,   S p <- S rt + beta (S p)
+ * replaces the matvec S p of the next iteration.  alpha = eta / (p . Sp) and the exit test
+ * are unchanged (two inner products per iteration, as the reference's iteration has).  Same
+ * iterates in exact arithmetic; unlike the single-reduction form above no scalar is replaced
+ * by a recurrence, only the vector S p.  This is the checker of the product's
+ * MPCB200_PCG_VARIANT=2 kernels (the default of the single-CTA tilings); oracle_pcg stays the statement of the reference's
+ * iteration and the parity criteria (oracle/parity.py) are asserted against THAT one.
+ * ------------------------------------------------------------------------- */
+void F(oracle_pcg_sprec)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,
+                         REAL *lambda, unsigned max_iter, REAL exit_tol,
+                         unsigned *iters_out, unsigned char *max_iter_exit_out)
+{
+    const size_t n = (size_t)s * N;
+    REAL *r = (REAL *)calloc(n * 5, sizeof(REAL));
+    REAL *p = r + n, *q = p + n, *rt = q + n, *w = rt + n;   /* q = S p */
+    REAL eta, eta_new, alpha, beta, v;
+    unsigned iter = 0;
+    unsigned char max_iter_exit = 1;
+    size_t i;
+
+    F(oracle_bdmv)(s, N, S, lambda, w);
+    for (i = 0; i < n; i++) r[i] = gamma[i] - w[i];
+    F(oracle_bdmv)(s, N, Pinv, r, rt);
+    for (i = 0; i < n; i++) p[i] = rt[i];
+    eta = F(dot)(n, r, rt);
+    F(oracle_bdmv)(s, N, S, p, q);
+    for (iter = 0; iter < max_iter; iter++) {
+        v = F(dot)(n, p, q);
+        if (v == (REAL)0) { max_iter_exit = 0; break; }
+        alpha = eta / v;
+        for (i = 0; i < n; i++) { lambda[i] += alpha * p[i]; r[i] -= alpha * q[i]; }
+        F(oracle_bdmv)(s, N, Pinv, r, rt);
+        F(oracle_bdmv)(s, N, S, rt, w);                      /* overlaps the reduction below */
+        eta_new = F(dot)(n, r, rt);
+        if (FABS(eta_new) < exit_tol) { iter++; max_iter_exit = 0; break; }
+        beta = eta_new / eta;
+        eta = eta_new;
+        for (i = 0; i < n; i++) { p[i] = rt[i] + beta * p[i]; q[i] = w[i] + beta * q[i]; }
     }
     *iters_out = iter;
     *max_iter_exit_out = max_iter_exit;
