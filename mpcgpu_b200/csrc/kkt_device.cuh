@@ -35,12 +35,14 @@ namespace mpcb200 {
 #define MPCB200_PINV_TMEM 1   // 0: Pinv rows stay in shared memory during the PCG phase (A/B builds)
 #endif
 #ifndef MPCB200_PCG_VARIANT
-// iteration of pcg_rows: 0 = the two-reduction PCG as the reference states it (every tiling);
-//   1 = single-reduction PCG (Chronopoulos-Gear; fails the +-1 iteration criterion on two real-IIWA solves: A/B builds only);
-//   2 = S p carried by a recurrence so that the r.rt reduction hides behind the matvec S rt -- single-CTA tilings (the
-//       batched path); cluster and knot-split tilings run 0.  Same exit test, same two inner products; meets the
-//       operating-point parity criteria asserted against the reference's iteration.
-#define MPCB200_PCG_VARIANT 2
+// iteration of pcg_rows: 0 = the two-reduction PCG as the reference states it (the default, every tiling);
+//   1 = single-reduction PCG (Chronopoulos-Gear; fails the +-1 iteration criterion on two real-IIWA solves);
+//   2 = S p carried by a recurrence so that the r.rt reduction hides behind the matvec S rt (single-CTA tilings; cluster and
+//       knot-split tilings run 0).  4 % faster on the bench workload and within the operating-point criteria, but measured
+//       5-20x farther from the exact-arithmetic iterate than variant 0 at tight tolerances (tools/variant_drift.py,
+//       profiles/r2i_variant_drift_table.txt): the recurrence loses what the matvec S p would recompute.
+// 1 and 2 are A/B build options only; parity comes first.
+#define MPCB200_PCG_VARIANT 0
 #endif
 constexpr int pow2_at_least(int x) { int p = 32; while (p < x) p *= 2; return p; }
 
@@ -1205,11 +1207,18 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         put(pv + sl * VK, rt);
         part[tid] = dotp(rr, rt);
         __syncthreads();
+#ifdef MPCB200_V2_EXPOSED      // A/B builds: the same recurrence with the reduction NOT overlapped
+        const T eta_new = cluster_sum<CF>(red, mb, par, 1, part[tid], rank, hb);
+        s_mv(pv, y);
+        if (absT(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
+        const T beta = divT(eta_new, eta);
+#else
         AllSum<T, CF::NT> sum(part, eta);
         s_mv_h(pv, y, &sum);
         const T eta_new = sum.a;
         if (absT(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
         const T beta = sum.quot;
+#endif
         eta = eta_new;
 #pragma unroll
         for (int j = 0; j < RPT; j++) { pp[j] = fm(beta, pp[j], rt[j]); qq[j] = fm(beta, qq[j], y[j]); }

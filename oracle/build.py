@@ -39,8 +39,9 @@ HARNESS = os.path.join(RUN, "ref_harness")
 TRACK = os.path.join(RUN, "track_iiwa_pcg_n%d")
 TRACK_KNOTS = (32, 128)
 # the same unchanged source with the SQP wall-clock budget lifted (-DSQP_MAX_TIME_US, an #ifndef knob of the reference's
-# settings.cuh:173): under ncu every launch takes milliseconds and the 2 ms budget would end each SQP solve after its first
-# kernel, so the profiler's launch list is taken from this build
+# settings.cuh:173): under ncu every launch costs milliseconds and the stock 2 ms budget (even a 20 ms one) ends each SQP
+# solve before its PCG launch, so the profiler's launch list is taken from this build, on a shortened copy of the
+# trajectory files (tools/gpu_r2i.sh) so that the unprofiled run it must follow stays within minutes
 TRACK_NOLIMIT = os.path.join(RUN, "track_iiwa_pcg_n128_nolimit")
 SQPB = os.path.join(RUN, "sqp_batched_check")   # tools/sqp_batched_check.cu
 KKTB = os.path.join(RUN, "kkt_batched_check")   # tools/kkt_batched_check.cu

@@ -405,7 +405,7 @@ void F(oracle_pcg_cg1)(int s, int N, const REAL *S, const REAL *Pinv, const REAL
  * are unchanged (two inner products per iteration, as the reference's iteration has).  Same
  * iterates in exact arithmetic; unlike the single-reduction form above no scalar is replaced
  * by a recurrence, only the vector S p.  This is the checker of the product's
- * MPCB200_PCG_VARIANT=2 kernels (the default of the single-CTA tilings); oracle_pcg stays the statement of the reference's
+ * MPCB200_PCG_VARIANT=2 builds (an A/B option, not the default); oracle_pcg stays the statement of the reference's
  * iteration and the parity criteria (oracle/parity.py) are asserted against THAT one.
  * ------------------------------------------------------------------------- */
 void F(oracle_pcg_sprec)(int s, int N, const REAL *S, const REAL *Pinv, const REAL *gamma,

@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-2 GPU call H: full GPU suite on the new default (PCG variant 2 on the single-CTA tilings, 16 B vector loads, radix
+# round-2 GPU call H: full GPU suite on the final default (PCG variant 0; 16 B vector loads, radix
 # warp sums, L2 input prefetch), parity report, bench (+ reference arm), ncu launch lists (bench; the reference's closed loop
 # on the L1 shim with the SQP wall-clock budget lifted) and one full capture of the fused kernel
 cd "$(dirname "$0")/.." || exit 1
@@ -15,7 +15,5 @@ timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > $O/${T}_benc
 timeout 300 python tools/quick_fused.py default > $O/${T}_quick_fused.jsonl 2>&1
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${T}_launches.csv python bench.py --steps 2 --warmup 3 --no-extras > $O/${T}_ncu1.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:fused_kernel -s 4 -c 1 -f -o $O/${T}_fused python tools/quick_fused.py --child default > $O/${T}_ncu2.log 2>&1
-( cd oracle/_ref/run
-  timeout 300 ./track_iiwa_pcg_n128_nolimit > ../../../$O/${T}_l1_nolimit_plain.log 2>&1
-  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -s 300 -c 120 --csv --log-file ../../../$O/${T}_l1_track_n128_launches.csv ./track_iiwa_pcg_n128_nolimit > ../../../$O/${T}_l1_ncu.log 2>&1 )
+bash tools/gpu_r2i.sh ${T} > $O/${T}_r2i.log 2>&1
 echo done
