@@ -162,8 +162,17 @@ __device__ __forceinline__ T warp_sum_radix(T a) {
     const T u1 = __shfl_xor_sync(0xffffffffu, b, 8), u2 = __shfl_xor_sync(0xffffffffu, b, 16), u3 = __shfl_xor_sync(0xffffffffu, b, 24);
     return (b + u1) + (u2 + u3);
 }
-__device__ __forceinline__ float warp_sum(float v) { return warp_sum_radix(v); }
-__device__ __forceinline__ double warp_sum(double v) { return warp_sum_radix(v); }
+#ifndef MPCB200_WARP_SUM_BUTTERFLY
+#define MPCB200_WARP_SUM_BUTTERFLY 0      // 1: the five-level butterfly (A/B builds)
+#endif
+template <class T>
+__device__ __forceinline__ T warp_sum_butterfly(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) { return MPCB200_WARP_SUM_BUTTERFLY ? warp_sum_butterfly(v) : warp_sum_radix(v); }
+__device__ __forceinline__ double warp_sum(double v) { return MPCB200_WARP_SUM_BUTTERFLY ? warp_sum_butterfly(v) : warp_sum_radix(v); }
 
 // ---- row tiles ------------------------------------------------------------------------
 // write my row (D values, zero padded to a multiple of 4) to dst + row*ld

@@ -849,21 +849,23 @@ __device__ __forceinline__ float sys_poll_tagged(const SplitCtx& X, const uint2*
 // 7 column-pair steps of a matvec: the loads, the lane's own tree and the 5 butterfly levels then sit between
 // independent FFMA2s instead of in front of a waiting CTA.
 // ---------------------------------------------------------------------------------------
-// Column pair w = 0..6 of a 14-vector slot in shared memory (16 B aligned), asked for in ascending order: float slots are
-// fetched 16 B at a time (pairs w, w+1 together: 4 loads per block instead of 7 -- the matvecs are issue-bound).
-template <class T2> struct XVec;
-template <> struct XVec<float2> {
+// Column pair w = 0..6 of a 14-vector slot in shared memory (16 B aligned), asked for in ascending order.  WIDE: float slots
+// are fetched 16 B at a time (pairs w, w+1 together: 4 loads per block instead of 7).  That pays where the matvecs are
+// issue-bound (two or more warps per scheduler: 4096 x N=64 fused 3.16 -> 3.10 ms) and costs where they are latency-bound
+// (the 128-thread cluster tilings, one warp per scheduler: N=128 single PCG 89.4 -> 93.0 us), so the tiling chooses.
+template <class T2, bool WIDE> struct XVec;
+template <bool WIDE> struct XVec<float2, WIDE> {
     const float* v; float2 odd;
     __device__ __forceinline__ explicit XVec(const float* p) : v(p), odd(make_float2(0.f, 0.f)) {}
     __device__ __forceinline__ float2 get(int w) {
-        if (w == 6) return reinterpret_cast<const float2*>(v)[6];
+        if (!WIDE || w == 6) return reinterpret_cast<const float2*>(v)[w];
         if (w & 1) return odd;
         const float4 q = reinterpret_cast<const float4*>(v)[w >> 1];
         odd = make_float2(q.z, q.w);
         return make_float2(q.x, q.y);
     }
 };
-template <> struct XVec<double2> {
+template <bool WIDE> struct XVec<double2, WIDE> {
     const double2* v;
     __device__ __forceinline__ explicit XVec(const double* p) : v(reinterpret_cast<const double2*>(p)) {}
     __device__ __forceinline__ double2 get(int w) { return v[w]; }
@@ -1000,7 +1002,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     // there (round 1: all of Pinv, none of S) neither matvec is bound by it.
     T2 Pd[TM ? RPT : 1][7];
     auto s_mv_h = [&](const T* vec, T (&y)[RPT], AllSum<T, CF::NT>* hook) {   // hook->step(w): independent work spread over the 7 steps
-        XVec<T2> vl(vec + (sl - 1) * VK), vd(vec + sl * VK), vr(vec + (sl + 1) * VK);
+        XVec<T2, (CF::NT > 128)> vl(vec + (sl - 1) * VK), vd(vec + sl * VK), vr(vec + (sl + 1) * VK);
         T2 acc[RPT];
 #pragma unroll
         for (int j = 0; j < RPT; j++) acc[j] = splat(T(0));
@@ -1035,7 +1037,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     };
     auto s_mv = [&](const T* vec, T (&y)[RPT]) { s_mv_h(vec, y, nullptr); };
     auto pinv_mv = [&](const T* vec, T (&y)[RPT]) {
-        XVec<T2> vl(vec + (sl - 1) * VK), vd(vec + sl * VK), vr(vec + (sl + 1) * VK);
+        XVec<T2, (CF::NT > 128)> vl(vec + (sl - 1) * VK), vd(vec + sl * VK), vr(vec + (sl + 1) * VK);
         T2 acc[RPT];
 #pragma unroll
         for (int j = 0; j < RPT; j++) acc[j] = splat(T(0));
