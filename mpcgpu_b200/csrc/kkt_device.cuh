@@ -749,13 +749,16 @@ __device__ __forceinline__ void st_async_pair(uint32_t a, float x, float y, uint
 }
 __device__ __forceinline__ void st_async_pair(uint32_t a, double x, double y, uint32_t mb) { st_async_f64(a, x, mb); st_async_f64(a + 8u, y, mb); }
 
-template <class CF>
+// RADIX: warp sums as radix-8 + radix-4 exchanges (common.cuh).  Measured: faster in the single-GPU kernels (4096 x N=64
+// fused -1.7 %, N=128 cluster PCG -2.2 %), SLOWER in the knot-split kernel (2 GPUs, N=512: 7.7 -> 8.6 us per iteration,
+// profiles/r2o_knotsplit_ab.txt), which therefore keeps the five-level butterfly.
+template <class CF, bool RADIX = true>
 __device__ __forceinline__ typename CF::T cluster_sum(typename CF::T* red, uint64_t* mb, unsigned (&par)[2], int buf,
                                                       typename CF::T val, unsigned rank, unsigned halo_bytes) {
     using T = typename CF::T;
     constexpr int CL = CF::CL, NW = CF::NW, NRED = CF::NRED;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const T w = warp_sum(val);
+    const T w = RADIX ? warp_sum(val) : warp_sum_butterfly(val);
     T* slot = red + buf * CF::NREDP + rank * NW + warp;
     if constexpr (CL == 1) {
         if (lane == 0) *slot = w;
@@ -778,7 +781,7 @@ __device__ __forceinline__ typename CF::T cluster_sum(typename CF::T* red, uint6
             if (lane < NRED / 4) {
                 acc = sum4(red + buf * CF::NREDP + 4 * lane);
             }
-            return warp_sum(acc);
+            return RADIX ? warp_sum(acc) : warp_sum_butterfly(acc);
         }
     }
 }
@@ -1109,7 +1112,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         T v = T(0);
         if (lane < (int)X->world) v = sys_poll_tagged(*X, X->mail[X->grank] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + lane, tag);
         __syncwarp();
-        return warp_sum(v);
+        return warp_sum_butterfly(v);
     };
     auto dotp = [&](const T (&a)[RPT], const T (&b)[RPT]) {
         T d = T(0);
@@ -1317,7 +1320,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
     if (first_g) { if (has_l) push(hr_p, rank - 1, 1, pp); else if (gl) gpush(4, 1, X->grank - 1, tg0, pp); else put(hl_p, zero); }
     if (last_g)  { if (has_r) push(hl_p, rank + 1, 1, pp); else if (gr) gpush(4, 0, X->grank + 1, tg0, pp); else put(hr_p, zero); }
     if (SPLIT) gpull_rows(4, tg0, hl_p, hr_p);
-    T eta = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+    T eta = cluster_sum<CF, !SPLIT>(red, mb, par, 1, dotp(rr, rt), rank, hb);
     if (SPLIT) eta = gsum(1, ++gseq[1], eta);
     // the p rows stored above are read by OTHER warps in the first S p: for CL > 1 the reduction ends on an
     // mbarrier wait, which orders the st.async bytes only, so the ordinary stores need a CTA barrier of their own
@@ -1335,7 +1338,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
             if (first_g && gl) gpush(0, 1, X->grank - 1, gseq[0] + 1, y);
             if (last_g && gr)  gpush(0, 0, X->grank + 1, gseq[0] + 1, y);
         }
-        T v = cluster_sum<CF>(red, mb, par, 0, dotp(pp, y), rank, hb);
+        T v = cluster_sum<CF, !SPLIT>(red, mb, par, 0, dotp(pp, y), rank, hb);
         if (SPLIT) v = gsum(0, ++gseq[0], v);
         if (v == T(0)) { max_iter_exit = false; break; }
         const T alpha = divT(eta, v);
@@ -1371,7 +1374,7 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
             if (first_g && gl) gpush(1, 1, X->grank - 1, gseq[1] + 1, rt);
             if (last_g && gr)  gpush(1, 0, X->grank + 1, gseq[1] + 1, rt);
         }
-        T eta_new = cluster_sum<CF>(red, mb, par, 1, dotp(rr, rt), rank, hb);
+        T eta_new = cluster_sum<CF, !SPLIT>(red, mb, par, 1, dotp(rr, rt), rank, hb);
         if (SPLIT) eta_new = gsum(1, ++gseq[1], eta_new);
         if (absT(eta_new) < exit_tol) { iter++; max_iter_exit = false; break; }
         const T beta = divT(eta_new, eta);
