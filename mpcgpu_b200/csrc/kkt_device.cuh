@@ -414,19 +414,32 @@ __device__ __forceinline__ void schur_rows(typename CF::T* smem, const KktPtrs<t
         }
         aR[j][7] = T(0);
     }
-    __syncthreads();                               // staging done (vectors overwrite zeroed chunks)
+    // the vector entries are fetched BEFORE the barrier (their round trip overlaps the block loads above: fused 4096 x 64
+    // 3.053 -> 3.024 ms) and parked in shared memory after it (the vectors overwrite chunks the staging loop zeroes).
+    // Issuing the G row loads ahead of the staging loop as well was slower (Schur phase 0.875 -> 0.896 ms).
+    T gq[RPT], gqm[RPT], gc[RPT], grm[RPT7];
+#pragma unroll
+    for (int j = 0; j < RPT; j++) {
+        const int r = rm.row[j];
+        gq[j] = (rm.ok[j] && valid) ? __ldg(P.g + (size_t)k * gSET + r) : T(0);
+        gqm[j] = (rm.ok[j] && inner) ? __ldg(P.g + (size_t)(k - 1) * gSET + r) : T(0);
+        gc[j] = (rm.ok[j] && inner) ? __ldg(P.c + (size_t)k * S + r) : T(0);
+    }
+#pragma unroll
+    for (int j = 0; j < RPT7; j++) grm[j] = (rm7.ok[j] && inner) ? __ldg(P.g + (size_t)(k - 1) * gSET + S + rm7.row[j]) : T(0);
+    __syncthreads();                               // staging done
 #pragma unroll
     for (int j = 0; j < RPT; j++) {
         if (rm.ok[j]) {
             const int r = rm.row[j];
-            vq[r] = valid ? __ldg(P.g + (size_t)k * gSET + r) : T(0);
-            vqm[r] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + r) : T(0);
-            vc[r] = inner ? __ldg(P.c + (size_t)k * S + r) : T(0);
+            vq[r] = gq[j];
+            vqm[r] = gqm[j];
+            vc[r] = gc[j];
         }
     }
 #pragma unroll
     for (int j = 0; j < RPT7; j++)
-        if (rm7.ok[j]) vrm[rm7.row[j]] = inner ? __ldg(P.g + (size_t)(k - 1) * gSET + S + rm7.row[j]) : T(0);
+        if (rm7.ok[j]) vrm[rm7.row[j]] = grm[j];
     if (t == 0) vrm[7] = T(0);
     // knot 0: Pinv[0][1] = -Qt_0, stored BEFORE inversion (linsys_setup.cuh:202-210); its A
     // tile is unused, park the rows there
@@ -437,7 +450,8 @@ __device__ __forceinline__ void schur_rows(typename CF::T* smem, const KktPtrs<t
 
     // ---- phase 1a: inverses ---------------------------------------------------------------
     gj14<LPK, RPT>(aQ, t, piv);                                        // Qt_k^-1
-    gj7<LPK, RPT7>(aR, t, piv);                                        // Rt_{k-1}^-1
+    gj7<LPK, RPT7>(aR, t, piv);                                        // Rt_{k-1}^-1   (the two loops merged into one pivot loop,
+                                                                       //  14 steps instead of 21: same bits, no faster)
 #pragma unroll
     for (int j = 0; j < RPT; j++) {
         if (valid && rm.ok[j]) {
