@@ -453,6 +453,22 @@ def parity_block(N, d, lam, it, ex, tol, samples):
     return out
 
 
+def variant2_leg():
+    """Informational: the same workload with MPCGPU_B200_PCG_VARIANT=2 (read once per process, hence a child process:
+    tools/quick_fused.py).  Not the default and not the headline: DESIGN.md 3 has the accuracy it costs."""
+    import subprocess
+    env = dict(os.environ, MPCGPU_B200_PCG_VARIANT="2")
+    try:
+        r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "quick_fused.py"), "--child", "variant2"], env=env,
+                           capture_output=True, text=True, timeout=300)
+        out = json.loads([l for l in r.stdout.splitlines() if l.startswith("{")][-1])
+    except Exception as e:      # informational leg: never fails the bench line
+        return {"error": str(e)[:200]}
+    return {"kernel_ms": out["kernel_ms"], "solves_per_s": out["solves_per_s"], "iters_sum": out["iters_sum"],
+            "note": "opt-in (MPCGPU_B200_PCG_VARIANT=2): S p by recurrence, r.rt reduction hidden behind the matvec; meets the operating-point "
+                    "criteria but is 5-20x farther from the exact-arithmetic iterate than the default at tight tolerances"}
+
+
 def warm_start_leg(torch, mg, N, B, G, G0, Cm, g, cv, rho, lam_star, it, ex, tol, steps):
     """the reference's operating point is a warm-started lambda (include/mpcsim.cuh:227,383).  Same batch,
     lambda0 = lambda* (1 + N(0, 1e-2)) with lambda* = the reference QDLDL solutions; kernel time by CUDA events."""
@@ -686,6 +702,7 @@ def main():
                 line["two_stage"] = two_stage_batched(torch, mg, N, B, G0, Cm, g, cv, rho, a.tol, peak)
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
                 line["f64"] = f64_leg(torch, mg, N, min(B, 1024), a.tol)
+                line["pcg_variant2_opt_in"] = variant2_leg()
         line["e2e_producer"] = ep
         if per_rank is not None:
             line["per_rank"] = per_rank

@@ -58,6 +58,11 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
         const char* e = getenv("MPCGPU_B200_LATENCY_TILING");
         return e ? atoi(e) : -1;      // -1: automatic, 0: never, 1: always
     }();
+    static const bool var2 = [] {     // opt-in: PCG variant 2 in the fused kernel of the 64-knot throughput tiling
+        const char* e = getenv("MPCGPU_B200_PCG_VARIANT");
+        return e && atoi(e) == 2;
+    }();
+    (void)var2;
     const int N = a.N;
 #ifdef MPCB200_MINIMAL   // experiment builds (tools/ab_build.sh): the bench tiling only, a minute of nvcc
 #ifdef MPCB200_MIN64_K     // the tiling under test for N <= 64 (default: the bench tiling)
@@ -83,7 +88,10 @@ cudaError_t dispatch(const BatchArgs& a, cudaStream_t st) {
     if (N <= 16) return launch<Cfg<16, 1, 8>, KIND>(a, st);
     if (N <= 32) return launch<Cfg<32, 1, 8>, KIND>(a, st);
     if (lpk == 4) {
-        if (N <= 64) return launch<Cfg<64, 1, 4>, KIND>(a, st);
+        if (N <= 64) {
+            if (KIND == K_FUSED && var2) return launch<Cfg<64, 1, 4>, K_FUSED_V2>(a, st);
+            return launch<Cfg<64, 1, 4>, KIND>(a, st);
+        }
         if (N <= 128) return launch<Cfg<64, 2, 4>, KIND>(a, st);
     } else {
         if (N <= 64) return launch<Cfg<64, 1, 8>, KIND>(a, st);

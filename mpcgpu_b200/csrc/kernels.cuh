@@ -177,7 +177,7 @@ __device__ __forceinline__ void prefetch_inputs_l2(const BatchArgsT<typename CF:
     pf(a.lambda + b * a.sv, a.sv);
 }
 
-template <class CF>
+template <class CF, int VAR = MPCB200_PCG_VARIANT>
 __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgsT<typename CF::T> a) {
     extern __shared__ float4 smem4[];
     using T = typename CF::T;
@@ -187,8 +187,8 @@ __global__ void __launch_bounds__(CF::NT, CF::MIN_CTAS) fused_kernel(BatchArgsT<
     RowsOf<CF> R;
     schur_rows<CF>(smem, P, a.N, a.rho_dev ? __ldg(a.rho_dev + b * a.rho_stride) : a.rho, R);
     if (CF::CL == 1 && a.pf_dist > 0) prefetch_inputs_l2<CF>(a, (long long)b + a.pf_dist);
-    pcg_rows<CF>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
-                 a.exits + b);
+    pcg_rows<CF, false, VAR>(smem, R, a.lambda + b * a.sv, a.N, a.max_iter, a.exit_tol, a.iters + b,
+                             a.exits + b);
     if (a.dz) {   // compute_dz epilogue: lambda and G^-1 were written by this cluster, read back through L2
         if (CF::CL == 1) __syncthreads();   // CL > 1: pcg_rows ended on a cluster barrier (release/acquire)
         dz_rows(P.G, P.C, P.g, a.lambda + b * a.sv, a.dz + b * a.sdz, a.N, (int)cluster_rank<CF::CL>() * CF::KPC, CF::KPC);

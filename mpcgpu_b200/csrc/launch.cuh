@@ -10,11 +10,13 @@
 
 namespace mpcb200 {
 
-enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2 };
+// K_FUSED_V2: the fused kernel with PCG variant 2 (S p by recurrence, hidden r.rt reduction) -- an opt-in of the bench
+// tiling only (MPCGPU_B200_PCG_VARIANT=2 in the environment; see kkt_device.cuh and DESIGN.md 3 for what it costs in accuracy)
+enum Kind { K_SCHUR = 0, K_PCG = 1, K_FUSED = 2, K_FUSED_V2 = 3 };
 
 template <class CF, int KIND>
 cudaError_t launch(const BatchArgsT<typename CF::T>& a, cudaStream_t st) {
-    auto kern = (KIND == K_SCHUR) ? schur_kernel<CF> : (KIND == K_PCG) ? pcg_kernel<CF> : fused_kernel<CF>;
+    auto kern = (KIND == K_SCHUR) ? schur_kernel<CF> : (KIND == K_PCG) ? pcg_kernel<CF> : (KIND == K_FUSED_V2) ? fused_kernel<CF, 2> : fused_kernel<CF>;
     static thread_local int configured_dev = -1;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
@@ -42,7 +44,7 @@ cudaError_t launch(const BatchArgsT<typename CF::T>& a, cudaStream_t st) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     BatchArgsT<typename CF::T> args = a;
-    if (KIND == K_FUSED && CF::CL == 1) {
+    if ((KIND == K_FUSED || KIND == K_FUSED_V2) && CF::CL == 1) {
         // batches of more than one wave: instance b prefetches the inputs of instance b + (CTAs resident at once) into L2
         static thread_local int resident = 0;
         static const bool on = [] { const char* v = getenv("MPCGPU_B200_L2_PREFETCH"); return !(v && v[0] == '0'); }();
