@@ -5,6 +5,7 @@ cd "$(dirname "$0")/.." || exit 1
 export LD_LIBRARY_PATH=/usr/local/cuda/lib64:$LD_LIBRARY_PATH
 O=$PWD/gpurun_out; T=${1:-r2i}
 mkdir -p $O
+# libexp_m2.so: tools/ab_build.sh m2 -DMPCB200_PCG_VARIANT=2 (the run-time opt-in covers the fused kernel only; this tool drives the PCG kernel)
 timeout 900 python tools/variant_drift.py default m2 > $O/${T}_variant_drift.jsonl 2> $O/${T}_variant_drift.err
 R=oracle/_ref/run
 mkdir -p $R/short/examples/trajfiles $R/short/tmp/results
