@@ -362,6 +362,50 @@ def knotsplit_bench(torch, mg, dist, rank, world, dev, N, tol, grp, reps=30, che
     return out
 
 
+def long_horizon_one_gpu(torch, mg, dev, N, clusters, tol, reps=20):
+    """Horizons beyond one cluster on ONE GPU: the knot-split kernel with all `clusters` knot ranges resident on this device
+    (one cooperative launch of `clusters` clusters of 16 CTAs, 512 knots each; the mailboxes are local, the exchange goes
+    through L2 instead of NVLink).  No single-cluster entry point takes N > 512.  Stream-timed; iteration count and lambda
+    against the oracle PCG on the GPU's own S / Pinv / gamma rows."""
+    import oracle
+    from mpcgpu_b200 import synth
+    d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + N)
+    t1 = lambda a: torch.from_numpy(np.ascontiguousarray(a))
+    rows = [mg.schur_rows_local(S, C, N, r, clusters, t1(d["G"][0]), t1(d["C"][0]), t1(d["g"][0]), t1(d["c"][0]), d["rho"]) for r in range(clusters)]
+    Sg = torch.cat([r[0] for r in rows]); Pg = torch.cat([r[1] for r in rows]); gam = torch.cat([r[2] for r in rows])
+    mail = torch.zeros((clusters, mg.mailbox_bytes() // 4), dtype=torch.int32, device=dev)
+    ptrs = [mail[r].data_ptr() for r in range(clusters)]
+    it = torch.zeros(clusters, dtype=torch.int32, device=dev); ex = torch.zeros(clusters, dtype=torch.uint8, device=dev)
+    lam = torch.zeros(S * N, device=dev)
+    cfg = mg.PcgConfig(pcg_exit_tol=tol)
+    stride = mg.epoch_stride(cfg)
+    epoch = 0
+
+    def solve():
+        nonlocal epoch
+        lam.zero_()
+        mg.knotsplit_pcg(S, N // clusters, clusters, 0, clusters, epoch, ptrs, Sg, Pg, gam, lam, it, ex, cfg)
+        epoch += stride
+    for _ in range(3):
+        solve()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        solve()
+    e1.record(); torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) / reps * 1e3
+    iters = int(it[0].item())
+    Sn, Pn, gn, l0 = Sg.cpu().numpy(), Pg.cpu().numpy(), gam.cpu().numpy(), np.zeros(S * N, np.float32)
+    _, it_o, _ = oracle.pcg(S, N, Sn, Pn, gn, l0, 10000, tol)
+    lam_s, _, _ = oracle.pcg(S, N, Sn, Pn, gn, l0, iters, 0.0)
+    floor = float(oracle.pcg_noise_floor(S, N, Sn, Pn, gn, l0, iters))
+    relv = float(np.linalg.norm(lam.cpu().numpy() - lam_s) / np.linalg.norm(lam_s))
+    return {"knot_points": N, "clusters": clusters, "solve_us": us, "iters": iters, "us_per_iter": us / max(iters, 1),
+            "max_iter_exit": int(ex.sum().item()), "oracle_iters": int(it_o), "lambda_rel_vs_oracle_same_iters": relv,
+            "fp32_floor": floor, "within_max_1e-4_3x_floor": bool(relv <= max(1e-4, 3.0 * floor) and abs(iters - it_o) <= 1)}
+
+
 def nccl_exchange_floor(torch, dist, rank, world, dev, iters=200):
     """SURVEY 8(e) "baseline to beat": what the knot split's two exchanges per PCG iteration cost when they go through
     NCCL -- all_reduce of the partial sums + send/recv of the 14-float boundary rows to both neighbours, twice per
@@ -703,6 +747,7 @@ def main():
                 line["single_solve"] = [single_solve_latency(torch, mg, n, a.tol) for n in (64, 128, 512)]
                 line["f64"] = f64_leg(torch, mg, N, min(B, 1024), a.tol)
                 line["pcg_variant2_opt_in"] = variant2_leg()
+                line["long_horizon_one_gpu"] = [long_horizon_one_gpu(torch, mg, dev, n, c, a.tol) for n, c in ((1024, 2), (2048, 4))]
         line["e2e_producer"] = ep
         if per_rank is not None:
             line["per_rank"] = per_rank
