@@ -1120,13 +1120,29 @@ __device__ __forceinline__ void pcg_rows(typename CF::T* smem, const RowsOf<CF>&
         }
     };
     // all-reduce of the per-rank totals (w is already identical in every thread of this cluster)
+#ifndef MPCB200_SPLIT_POLL1
+#define MPCB200_SPLIT_POLL1 1     // 1: ONE warp per CTA polls the mailbox and hands the sum to the others through shared memory
+#endif
     auto gsum = [&](int buf, unsigned tag, T w) {
         if (rank == 0 && tid < (int)X->world) sys_store_tagged(X->mail[tid] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + X->grank, w, tag);
         const int lane = tid & 31;
-        T v = T(0);
-        if (lane < (int)X->world) v = sys_poll_tagged(*X, X->mail[X->grank] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + lane, tag);
-        __syncwarp();
-        return warp_sum_butterfly(v);
+        if constexpr (MPCB200_SPLIT_POLL1) {
+            T* bc = smem + CF::oTm + 1 + buf;          // two spare words beside the tensor-memory base address
+            if (tid < 32) {
+                T v = T(0);
+                if (lane < (int)X->world) v = sys_poll_tagged(*X, X->mail[X->grank] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + lane, tag);
+                __syncwarp();
+                v = warp_sum_butterfly(v);
+                if (lane == 0) *bc = v;
+            }
+            __syncthreads();
+            return *bc;
+        } else {
+            T v = T(0);
+            if (lane < (int)X->world) v = sys_poll_tagged(*X, X->mail[X->grank] + X->parity * SPLIT_HALF_U2 + buf * SPLIT_MAXW + lane, tag);
+            __syncwarp();
+            return warp_sum_butterfly(v);
+        }
     };
     auto dotp = [&](const T (&a)[RPT], const T (&b)[RPT]) {
         T d = T(0);

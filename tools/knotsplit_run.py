@@ -20,17 +20,10 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 dev = torch.device("cuda", local)
 d = synth.gen_kkt(N, 1, seed=synth.BASE_SEED + N)
 lo, hi = mg.knot_range(N, rank, world)
-lo_e, hi_e, off = mg.schur_slice(N, rank, world)
-ne, n = hi_e - lo_e, hi - lo
-ze = mg.sizes(S, C, ne)
-t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)[None]
-G0 = t(d["G"][0][lo_e * 245: lo_e * 245 + ze["G"]]); Cm = t(d["C"][0][lo_e * 294: lo_e * 294 + ze["C"]])
-g = t(d["g"][0][lo_e * 21: lo_e * 21 + ze["g"]]); cv = t(d["c"][0][lo_e * 14: lo_e * 14 + ze["c"]])
-Se = torch.empty((1, ze["S"]), device=dev); Pe = torch.empty_like(Se); ge = torch.empty((1, ze["gamma"]), device=dev)
-G = G0.clone()
-mg.form_schur_system(S, C, ne, G, Cm, g, cv, Se, Pe, ge, d["rho"])
-Sl = Se[0, off * 588:(off + n) * 588].contiguous(); Pl = Pe[0, off * 588:(off + n) * 588].contiguous()
-gl = ge[0, off * 14:(off + n) * 14].contiguous()
+n = hi - lo
+t1 = lambda a: torch.from_numpy(np.ascontiguousarray(a))
+# my rows of S / Pinv / gamma from my slice of the inputs, no communication (ranges of up to 512 knots)
+Sl, Pl, gl = mg.schur_rows_local(S, C, N, rank, world, t1(d["G"][0]), t1(d["C"][0]), t1(d["g"][0]), t1(d["c"][0]), d["rho"])
 lam = torch.zeros(n * 14, device=dev)
 it = torch.zeros(1, dtype=torch.int32, device=dev); ex = torch.zeros(1, dtype=torch.uint8, device=dev)
 cfg = mg.PcgConfig(pcg_exit_tol=1e-4)
