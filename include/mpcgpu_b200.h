@@ -74,7 +74,10 @@ int mpcgpu_b200_pcg_f32(uint32_t state_size, uint32_t knot_points, uint32_t batc
                         uint8_t* d_max_iter_exit, void* d_ws, void* stream);
 
 /* Fused form_schur_system + pcg (include/pcg/sqp.cuh:243-277 as ONE launch): reads
- * G, C, g, c, lambda0; writes lambda, G^-1, iters, flags.  S and Pinv stay on-chip. */
+ * G, C, g, c, lambda0; writes lambda, G^-1, iters, flags.  S and Pinv stay on-chip.
+ * The iteration is the reference's two-reduction PCG.  Opt-in, read once per process: MPCGPU_B200_PCG_VARIANT=2 in the
+ * environment makes the batched 64-knot tiling carry S p by a recurrence (4 % faster; same exit test and criteria, but
+ * farther from the exact-arithmetic iterate at tight tolerances -- DESIGN.md 3).  No counterpart in the reference. */
 int mpcgpu_b200_kkt_solve_f32(uint32_t state_size, uint32_t control_size, uint32_t knot_points,
                               uint32_t batch, float* d_G, const float* d_C, const float* d_g,
                               const float* d_c, float rho, float* d_lambda, uint32_t max_iter,
